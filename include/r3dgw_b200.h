@@ -1,0 +1,222 @@
+/*
+ * r3dgw_b200.h - C-ABI of the B200-native (sm_100a) Gaussian-splat rasterizer + SH relighting path.
+ *
+ * This is the drop-in boundary for the reference's native layer.  Every entry point takes plain
+ * device pointers, sizes and a CUDA stream (passed as void* == cudaStream_t); no torch types.
+ * All functions return 0 on success, a positive cudaError_t value on a CUDA failure, or a negative
+ * R3DGW_ERR_* code on misuse.  Nothing is retained across calls except what the caller-owned state
+ * buffers hold (same ownership model as the reference: the caller allocates through callbacks and
+ * hands the opaque buffers back to the backward call).
+ *
+ * Reference interfaces replaced (paths relative to /root/reference/submodules):
+ *   r3dgw_rasterize_forward   <- CudaRasterizer::Rasterizer::forward   diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:34-57
+ *   r3dgw_rasterize_backward  <- CudaRasterizer::Rasterizer::backward  diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:59-86
+ *   r3dgw_mark_visible        <- CudaRasterizer::Rasterizer::markVisible diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:27-32
+ *   r3dgw_knn_dist2           <- SimpleKNN::knn                         simple-knn/simple_knn.h:18 (simple_knn.cu:185-221)
+ *   r3dgw_shade_forward/backward <- EnvironmentLight.shade + sky eval_sh  scene/NVDIFFREC/light.py:131-193,
+ *                                   gaussian_renderer/__init__.py:132-156 (torch graph in the reference)
+ * The staged entry points (geometry / blend) are the same pipeline split at the point where the
+ * reference's six per-render calls repeat identical work (gaussian_renderer/__init__.py:160-264).
+ */
+#ifndef R3DGW_B200_H_INCLUDED
+#define R3DGW_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define R3DGW_ERR_BAD_ARG      (-1)  /* null pointer / negative size / bad combination            */
+#define R3DGW_ERR_UNSUPPORTED  (-2)  /* channel count not instantiated, SH degree > 3, ...        */
+#define R3DGW_ERR_ALLOC        (-3)  /* an allocation callback returned NULL                      */
+#define R3DGW_ERR_OVERFLOW     (-4)  /* num_rendered would exceed 2^31-1 (reference cap, 32-bit)  */
+
+#define R3DGW_MAX_CHANNELS 32
+
+/* Allocation callback: must return a device pointer to >= bytes bytes, 256-B aligned, that stays
+ * valid until the matching backward call has returned (reference: resizeFunctional,
+ * diff-gaussian-rasterization/rasterize_points.cu:27-33). */
+typedef char* (*r3dgw_alloc_fn)(void* ctx, size_t bytes);
+
+/* Camera / raster settings shared by every stage (reference: the scalar tail of
+ * Rasterizer::forward's argument list; GaussianRasterizationSettings,
+ * diff_gaussian_rasterization/__init__.py:133-144).  All pointers are DEVICE pointers. */
+typedef struct r3dgw_camera {
+    int32_t width, height;
+    float tan_fovx, tan_fovy;
+    float scale_modifier;
+    int32_t prefiltered;
+    const float* viewmatrix;   /* 16 floats, column-major (already transposed by the caller)  */
+    const float* projmatrix;   /* 16 floats, column-major                                     */
+    const float* cam_pos;      /* 3 floats                                                    */
+} r3dgw_camera;
+
+/* Byte offsets of the sub-arrays inside the opaque state buffers, for tests and tooling. */
+typedef struct r3dgw_geom_layout {
+    size_t depths;         /* f32[P]     view-space z                                   */
+    size_t means2D;        /* float2[P]  pixel-space centre                             */
+    size_t conic_opacity;  /* float4[P]  (conic.x, conic.y, conic.z, opacity)           */
+    size_t cov3D;          /* f32[6P]                                                   */
+    size_t tiles_touched;  /* u32[P]                                                    */
+    size_t point_offsets;  /* u32[P]     inclusive prefix sum of tiles_touched          */
+    size_t rgb;            /* f32[3P]    SH->RGB result (only when shs are given)       */
+    size_t clamped;        /* u8[3P]                                                    */
+    size_t scan_state;     /* u64[blocks] decoupled look-back tile states               */
+    size_t total;
+} r3dgw_geom_layout;
+
+typedef struct r3dgw_binning_layout {
+    size_t point_list;          /* u32[R]   sorted Gaussian ids                          */
+    size_t point_list_keys;     /* u64[R]   sorted (tile<<32 | depth bits) keys          */
+    size_t point_list_alt;      /* u32[R]   ping-pong value buffer                       */
+    size_t point_list_keys_alt; /* u64[R]   ping-pong key buffer                         */
+    size_t ranges;              /* uint2[tiles]                                          */
+    size_t splats;              /* 2 x float4[R] sorted-order splat stream */
+    size_t sort_hist;           /* u32 radix histograms + look-back state                */
+    size_t total;
+} r3dgw_binning_layout;
+
+typedef struct r3dgw_image_layout {
+    size_t final_T;    /* f32[N] */
+    size_t n_contrib;  /* u32[N] */
+    size_t total;
+} r3dgw_image_layout;
+
+int r3dgw_get_geom_layout(int P, int has_sh, r3dgw_geom_layout* out);
+int r3dgw_get_binning_layout(int R, int width, int height, r3dgw_binning_layout* out);
+int r3dgw_get_image_layout(int width, int height, r3dgw_image_layout* out);
+
+/* Version / build info: returns a static string such as "r3dgw_b200 0.1 sm_100a". */
+const char* r3dgw_version(void);
+/* Number of kernel launches issued by this library in this process so far. */
+uint64_t r3dgw_launch_count(void);
+
+/* ---- staged pipeline ------------------------------------------------------------------------ */
+
+/* K1 preprocess (+fused prefix sum) -> D2H of num_rendered -> K2 duplicate -> onesweep radix sort
+ * -> K3 tile ranges + splat-stream gather.   Reference: rasterizer_impl.cu:216-318. */
+int r3dgw_geometry_forward(
+    r3dgw_alloc_fn geom_alloc, void* geom_ctx,
+    r3dgw_alloc_fn binning_alloc, void* binning_ctx,
+    int P, int D, int M,
+    const r3dgw_camera* cam,
+    const float* means3D, const float* shs, const float* opacities,
+    const float* scales, const float* rotations, const float* cov3D_precomp,
+    int* radii,            /* out, i32[P] */
+    int* num_rendered,     /* out, host   */
+    void* stream);
+
+/* K4: front-to-back blend of C-channel per-Gaussian features over the cached geometry.
+ * features == NULL selects the SH->RGB colours in the geometry buffer (C must be 3).
+ * Reference: FORWARD::render, forward.cu:261-374. */
+int r3dgw_blend_forward(
+    int P, int R, int C,
+    const r3dgw_camera* cam,
+    const char* geom_buffer, const char* binning_buffer, char* image_buffer,
+    const float* features,   /* f32[P,C] */
+    const float* background, /* f32[C]   */
+    float* out_color,        /* f32[C,H,W] */
+    void* stream);
+
+/* K5: backward of the blend; ACCUMULATES (+=) into dL_dmean2D[P,3], dL_dconic[P,4],
+ * dL_dopacity[P], dL_dfeatures[P,C] (caller zeroes them).  Reference: backward.cu:399-557. */
+int r3dgw_blend_backward(
+    int P, int R, int C,
+    const r3dgw_camera* cam,
+    const char* geom_buffer, const char* binning_buffer, const char* image_buffer,
+    const float* features, const float* background,
+    const float* dL_dpixels,  /* f32[C,H,W] */
+    float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dfeatures,
+    void* stream);
+
+/* K6+K7 fused: conic/mean2D gradients -> means3D, cov3D, scales, rotations (and SH).
+ * Overwrites dL_dmean3D/dL_dcov3D/dL_dscale/dL_drot rows of visible Gaussians (caller zeroes).
+ * Reference: BACKWARD::preprocess, backward.cu:144-396, 560-624. */
+int r3dgw_geometry_backward(
+    int P, int D, int M,
+    const r3dgw_camera* cam,
+    const float* means3D, const float* shs, const float* scales, const float* rotations,
+    const float* cov3D_precomp, const int* radii,
+    const char* geom_buffer,
+    const float* dL_dmean2D, const float* dL_dconic,
+    float* dL_dmean3D, float* dL_dcolor, float* dL_dcov3D, float* dL_dsh,
+    float* dL_dscale, float* dL_drot,
+    void* stream);
+
+/* ---- reference-shaped one-call entry points ------------------------------------------------- */
+
+int r3dgw_rasterize_forward(
+    r3dgw_alloc_fn geom_alloc, void* geom_ctx,
+    r3dgw_alloc_fn binning_alloc, void* binning_ctx,
+    r3dgw_alloc_fn image_alloc, void* image_ctx,
+    int P, int D, int M,
+    const float* background, const r3dgw_camera* cam,
+    const float* means3D, const float* shs, const float* colors_precomp, const float* opacities,
+    const float* scales, const float* rotations, const float* cov3D_precomp,
+    float* out_color, int* radii, int* num_rendered, void* stream);
+
+int r3dgw_rasterize_backward(
+    int P, int D, int M, int R,
+    const float* background, const r3dgw_camera* cam,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, const float* rotations, const float* cov3D_precomp,
+    const int* radii,
+    const char* geom_buffer, const char* binning_buffer, const char* image_buffer,
+    const float* dL_dpix,
+    float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+    float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+    void* stream);
+
+int r3dgw_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                       const float* projmatrix, uint8_t* present, void* stream);
+
+/* ---- simple-knn ------------------------------------------------------------------------------ */
+/* workspace: query bytes with r3dgw_knn_workspace_bytes(P); device memory owned by the caller. */
+size_t r3dgw_knn_workspace_bytes(int P);
+int r3dgw_knn_dist2(int P, const float* points /* f32[P,3] */, float* mean_dist2 /* f32[P] */,
+                    char* workspace, void* stream);
+
+/* ---- fused per-Gaussian relit shading ---------------------------------------------------------
+ * One thread per Gaussian.  For foreground Gaussians (is_sky[i]==0):
+ *   EnvironmentLight.shade (light.py:131-193): order-2 SH irradiance, optional SH-domain blurred
+ *   specular with the split-sum FG LUT, Fresnel mix, gamma.
+ * For sky Gaussians: clamp_min(eval_sh(1, sky_sh, dir) + 0.5, 0) or ones (fix_sky)
+ *   (gaussian_renderer/__init__.py:143-148).
+ * Material arrays (albedo/roughness/metalness) are indexed by FOREGROUND rank via fg_index[i]
+ * (the reference stores them for foreground Gaussians only).  fg_index may be NULL (identity).
+ * Outputs f32[P,3] each: rgb, diffuse, specular (sky rows of diffuse/specular are zero). */
+typedef struct r3dgw_shade_args {
+    int32_t P;
+    int32_t specular;      /* 0: Lambertian only (light.py:160-163) */
+    int32_t fix_sky;
+    int32_t sh_degree;     /* env SH degree (<=4 on the fused path) */
+    const float* positions;   /* f32[P,3] */
+    const float* normals;     /* f32[P,3] */
+    const float* albedo;      /* f32[Pfg,3] */
+    const float* roughness;   /* f32[Pfg]   */
+    const float* metalness;   /* f32[Pfg] or NULL */
+    const uint8_t* is_sky;    /* u8[P] or NULL */
+    const int32_t* fg_index;  /* i32[P] or NULL */
+    const float* cam_pos;     /* f32[3] device */
+    const float* env_sh;      /* f32[(deg+1)^2,3] device */
+    const float* sky_sh;      /* f32[4,3] device ([coef][channel]) or NULL */
+    const float* fg_lut;      /* f32[256,256,2] device */
+} r3dgw_shade_args;
+
+int r3dgw_shade_forward(const r3dgw_shade_args* a, float* rgb, float* diffuse, float* specular,
+                        void* stream);
+/* Gradients w.r.t. normals, albedo, roughness, metalness, positions (through wo / sky dir),
+ * env_sh and sky_sh.  env/sky SH gradients are ACCUMULATED (+=) with atomics; the per-Gaussian
+ * ones are overwritten. Any output pointer may be NULL to skip it. */
+int r3dgw_shade_backward(const r3dgw_shade_args* a,
+                         const float* dL_drgb, const float* dL_ddiffuse, const float* dL_dspecular,
+                         float* dL_dpositions, float* dL_dnormals, float* dL_dalbedo,
+                         float* dL_droughness, float* dL_dmetalness,
+                         float* dL_denv_sh, float* dL_dsky_sh, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* R3DGW_B200_H_INCLUDED */

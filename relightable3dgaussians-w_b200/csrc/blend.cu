@@ -1,0 +1,409 @@
+// blend.cu - K4 / K5: tile-based front-to-back alpha blending of C-channel per-Gaussian features and
+// its backward, for sm_100a.
+//
+// Reference behaviour: renderCUDA fwd  diff-gaussian-rasterization/cuda_rasterizer/forward.cu:261-374
+//                      renderCUDA bwd  diff-gaussian-rasterization/cuda_rasterizer/backward.cu:399-557
+// B200-first structure (not the reference's):
+//  * each tile's Gaussians arrive as a CONTIGUOUS slice of the sorted-order splat stream built by K3
+//    (geometry.cu), so a round of 256/128 splats is fetched with two 1-D bulk async copies
+//    (cp.async.bulk -> SASS UBLKCP) completing on an mbarrier, double-buffered against the blend loop;
+//    the reference does a dependent id -> xy/conic gather per thread per round;
+//  * per-call features are staged in shared memory once per round (the reference re-reads them from
+//    global per contributing pixel);
+//  * a per-splat conservative threshold skips the exp for pairs that cannot reach alpha >= 1/255;
+//  * warps cover 8x4 pixel footprints; backward pre-reduces the 6+C partial gradients over the warp
+//    with a halving butterfly, parks them in warp-private shared slots, and issues ONE global
+//    atomic per (tile, Gaussian, component) instead of one per (pixel, Gaussian, component);
+//  * backward starts at the tile's deepest contributor instead of the end of the list.
+// Every decision (power > 0, alpha < 1/255, T*(1-alpha) < 1e-4) is evaluated with the reference's
+// expression trees so that n_contrib is bit-identical and colours agree to rounding.
+#include "common.cuh"
+#include "warp_reduce.cuh"
+
+namespace r3dgw {
+
+// ---- mbarrier / bulk-copy PTX wrappers ---------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// lane -> pixel inside the 16x16 tile: warp w covers the 8x4 block (w%2, w/2)
+__device__ __forceinline__ void tile_pixel(unsigned tid, unsigned& px, unsigned& py) {
+    unsigned lane = tid & 31, warp = tid >> 5;
+    px = (warp & 1) * 8 + (lane & 7);
+    py = (warp >> 1) * 4 + (lane >> 3);
+}
+
+// =================================================================================================
+// K4 forward
+// =================================================================================================
+constexpr int FWD_BATCH = 256;
+
+template <int C>
+struct FwdSmem {
+    float4 A[2][FWD_BATCH];
+    float4 B[2][FWD_BATCH];
+    float feat[2][FWD_BATCH * C];
+    uint64_t bar[2];
+};
+
+template <int C>
+__global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
+    const uint2* __restrict__ ranges, const float4* __restrict__ splatA, const float4* __restrict__ splatB,
+    int W, int H, const float* __restrict__ features, const float* __restrict__ bg_color,
+    float* __restrict__ final_T, uint32_t* __restrict__ n_contrib, float* __restrict__ out_color) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    FwdSmem<C>& s = *reinterpret_cast<FwdSmem<C>*>(smem_raw);
+    const unsigned tid = threadIdx.x;
+    unsigned lx, ly;
+    tile_pixel(tid, lx, ly);
+    const uint2 pix = {blockIdx.x * TILE_X + lx, blockIdx.y * TILE_Y + ly};
+    const uint32_t pix_id = W * pix.y + pix.x;
+    const float2 pixf = {(float)pix.x, (float)pix.y};
+    const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
+    bool done = !inside;
+
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + FWD_BATCH - 1) / FWD_BATCH;
+
+    if (tid == 0) {
+        mbar_init(&s.bar[0], 1);
+        mbar_init(&s.bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0 && rounds > 0) {
+        uint32_t cnt = (uint32_t)min(FWD_BATCH, total);
+        mbar_expect_tx(&s.bar[0], cnt * 32u);
+        bulk_g2s(s.A[0], splatA + range.x, cnt * 16u, &s.bar[0]);
+        bulk_g2s(s.B[0], splatB + range.x, cnt * 16u, &s.bar[0]);
+    }
+
+    float T = 1.0f;
+    uint32_t last_contributor = 0;
+    float Cacc[C];
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) Cacc[ch] = 0.f;
+
+    for (int i = 0; i < rounds; ++i) {
+        const int buf = i & 1;
+        const int cnt = min(FWD_BATCH, total - i * FWD_BATCH);
+        mbar_wait(&s.bar[buf], (uint32_t)(i >> 1) & 1u);
+        // stage this round's features (ids ride in B.w)
+        if ((int)tid < cnt) {
+            const uint32_t id = __float_as_uint(s.B[buf][tid].w);
+            const float* f = features + (size_t)id * C;
+#pragma unroll
+            for (int ch = 0; ch < C; ++ch) s.feat[buf][tid * C + ch] = f[ch];
+        }
+        // one barrier per round: publishes the features, retires the other buffer, and votes
+        const int num_done = __syncthreads_count(done);
+        if (num_done == TILE_PIX) break;
+        if (tid == 0 && i + 1 < rounds) {
+            const int nb = buf ^ 1;
+            uint32_t ncnt = (uint32_t)min(FWD_BATCH, total - (i + 1) * FWD_BATCH);
+            const size_t off = (size_t)range.x + (size_t)(i + 1) * FWD_BATCH;
+            mbar_expect_tx(&s.bar[nb], ncnt * 32u);
+            bulk_g2s(s.A[nb], splatA + off, ncnt * 16u, &s.bar[nb]);
+            bulk_g2s(s.B[nb], splatB + off, ncnt * 16u, &s.bar[nb]);
+        }
+        if (done) continue;
+        const uint32_t base = (uint32_t)i * FWD_BATCH;
+        for (int j = 0; j < cnt; ++j) {
+            const float4 a = s.A[buf][j];
+            const float4 b = s.B[buf][j];
+            const float2 d = {a.x - pixf.x, a.y - pixf.y};
+            const float power = -0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y;
+            if (power > 0.0f) continue;
+            if (power < b.z) continue;   // cannot reach alpha >= 1/255 (conservative, see K3)
+            const float alpha = min(0.99f, b.y * exp(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) {
+                done = true;
+                break;
+            }
+#pragma unroll
+            for (int ch = 0; ch < C; ++ch) Cacc[ch] += s.feat[buf][j * C + ch] * alpha * T;
+            T = test_T;
+            last_contributor = base + (uint32_t)j + 1u;
+        }
+    }
+
+    if (inside) {
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+#pragma unroll
+        for (int ch = 0; ch < C; ++ch) out_color[(size_t)ch * H * W + pix_id] = Cacc[ch] + T * bg_color[ch];
+    }
+}
+
+
+// =================================================================================================
+// K5 backward
+// =================================================================================================
+constexpr int BWD_WARPS = TILE_PIX / 32;
+
+template <int C, int BATCH>
+struct BwdSmem {
+    static constexpr int NV = 6 + C;
+    float4 A[2][BATCH];
+    float4 B[2][BATCH];
+    float feat[2][BATCH * C];
+    float acc[BWD_WARPS][BATCH * NV];
+    uint32_t mask[BWD_WARPS][(BATCH + 31) / 32];
+    uint32_t red[BWD_WARPS];
+    uint64_t bar[2];
+};
+
+template <int C, int BATCH>
+__global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
+    const uint2* __restrict__ ranges, const float4* __restrict__ splatA, const float4* __restrict__ splatB,
+    int W, int H, const float* __restrict__ bg_color, const float* __restrict__ features,
+    const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+    const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D,
+    float* __restrict__ dL_dopacity, float* __restrict__ dL_dfeatures) {
+    constexpr int NV = 6 + C;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BwdSmem<C, BATCH>& s = *reinterpret_cast<BwdSmem<C, BATCH>*>(smem_raw);
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned lx, ly;
+    tile_pixel(tid, lx, ly);
+    const uint2 pix = {blockIdx.x * TILE_X + lx, blockIdx.y * TILE_Y + ly};
+    const uint32_t pix_id = W * pix.y + pix.x;
+    const float2 pixf = {(float)pix.x, (float)pix.y};
+    const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
+
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const float T_final = inside ? final_Ts[pix_id] : 0;
+    float T = T_final;
+    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0;
+
+    // deepest contributor of the warp / tile: nothing behind it receives gradient
+    const uint32_t warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0) s.red[warp] = warp_last;
+    if (tid == 0) {
+        mbar_init(&s.bar[0], 1);
+        mbar_init(&s.bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    uint32_t tile_last = 0;
+#pragma unroll
+    for (int w = 0; w < BWD_WARPS; ++w) tile_last = max(tile_last, s.red[w]);
+    const int total = (int)min(range.y - range.x, tile_last);
+    const int rounds = (total + BATCH - 1) / BATCH;
+    if (rounds == 0) return;
+
+    if (tid == 0) {
+        const int cnt = min(BATCH, total);
+        const size_t off = (size_t)range.x + (size_t)(total - cnt);
+        mbar_expect_tx(&s.bar[0], (uint32_t)cnt * 32u);
+        bulk_g2s(s.A[0], splatA + off, (uint32_t)cnt * 16u, &s.bar[0]);
+        bulk_g2s(s.B[0], splatB + off, (uint32_t)cnt * 16u, &s.bar[0]);
+    }
+
+    float accum_rec[C], last_color[C], dL_dpixel[C];
+    float bg_dot_dpixel = 0;
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) {
+        accum_rec[ch] = 0.f;
+        last_color[ch] = 0.f;
+        dL_dpixel[ch] = inside ? dL_dpixels[(size_t)ch * H * W + pix_id] : 0.f;
+        bg_dot_dpixel += bg_color[ch] * dL_dpixel[ch];
+    }
+    float last_alpha = 0;
+    const float ddelx_dx = 0.5 * W;
+    const float ddely_dy = 0.5 * H;
+
+    for (int i = 0; i < rounds; ++i) {
+        const int buf = i & 1;
+        const int hi = total - i * BATCH;
+        const int cnt = min(BATCH, hi);
+        const int lo = hi - cnt;
+        mbar_wait(&s.bar[buf], (uint32_t)(i >> 1) & 1u);
+        if ((int)tid < cnt) {
+            const uint32_t id = __float_as_uint(s.B[buf][tid].w);
+            const float* f = features + (size_t)id * C;
+#pragma unroll
+            for (int ch = 0; ch < C; ++ch) s.feat[buf][tid * C + ch] = f[ch];
+        }
+        if (lane < (BATCH + 31) / 32) s.mask[warp][lane] = 0;
+        __syncthreads();   // features staged; previous round's flush finished -> acc / other buffer free
+        if (tid == 0 && i + 1 < rounds) {
+            const int nb = buf ^ 1;
+            const int nhi = total - (i + 1) * BATCH;
+            const int ncnt = min(BATCH, nhi);
+            const size_t off = (size_t)range.x + (size_t)(nhi - ncnt);
+            mbar_expect_tx(&s.bar[nb], (uint32_t)ncnt * 32u);
+            bulk_g2s(s.A[nb], splatA + off, (uint32_t)ncnt * 16u, &s.bar[nb]);
+            bulk_g2s(s.B[nb], splatB + off, (uint32_t)ncnt * 16u, &s.bar[nb]);
+        }
+
+        if ((uint32_t)lo < warp_last) {
+            uint32_t my_mask = 0;   // lane 0 collects contribution bits, 32 splats at a time
+            for (int jj = cnt - 1; jj >= 0; --jj) {
+                const uint32_t k = (uint32_t)(lo + jj);
+                if (k < warp_last) {
+                    const float4 a = s.A[buf][jj];
+                    const float4 b = s.B[buf][jj];
+                    const float2 d = {a.x - pixf.x, a.y - pixf.y};
+                    const float power = -0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y;
+                    bool valid = (k < last_contributor) && !(power > 0.0f) && !(power < b.z);
+                    float G = 0.f, alpha = 0.f;
+                    if (valid) {
+                        G = exp(power);
+                        alpha = min(0.99f, b.y * G);
+                        valid = !(alpha < 1.0f / 255.0f);
+                    }
+                    if (__any_sync(0xffffffffu, valid)) {
+                        float g[NV];
+#pragma unroll
+                        for (int q = 0; q < NV; ++q) g[q] = 0.f;
+                        if (valid) {
+                            T = T / (1.f - alpha);
+                            const float dchannel_dcolor = alpha * T;
+                            float dL_dalpha = 0.0f;
+#pragma unroll
+                            for (int ch = 0; ch < C; ++ch) {
+                                const float c = s.feat[buf][jj * C + ch];
+                                accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                                last_color[ch] = c;
+                                const float dL_dchannel = dL_dpixel[ch];
+                                dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
+                                g[6 + ch] = dchannel_dcolor * dL_dchannel;
+                            }
+                            dL_dalpha *= T;
+                            last_alpha = alpha;
+                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                            const float dL_dG = b.y * dL_dalpha;
+                            const float gdx = G * d.x;
+                            const float gdy = G * d.y;
+                            const float dG_ddelx = -gdx * a.z - gdy * a.w;
+                            const float dG_ddely = -gdy * b.x - gdx * a.w;
+                            g[0] = dL_dG * dG_ddelx * ddelx_dx;
+                            g[1] = dL_dG * dG_ddely * ddely_dy;
+                            g[2] = -0.5f * gdx * d.x * dL_dG;
+                            g[3] = -0.5f * gdx * d.y * dL_dG;
+                            g[4] = -0.5f * gdy * d.y * dL_dG;
+                            g[5] = G * dL_dalpha;
+                        }
+                        float* slot = &s.acc[warp][jj * NV];
+                        warp_reduce_multi<NV>(g, lane, [&](int vi, float v) { slot[vi] = v; });
+                        my_mask |= 1u << (jj & 31);
+                    }
+                }
+                if ((jj & 31) == 0) {
+                    if (lane == 0) s.mask[warp][jj >> 5] = my_mask;
+                    my_mask = 0;
+                }
+            }
+        }
+        __syncthreads();   // all warps' partial sums parked
+
+        // flush: one atomic per (splat, component) that received anything in this tile
+        for (int e = (int)tid; e < cnt * NV; e += TILE_PIX) {
+            const int jj = e / NV;
+            const int vi = e - jj * NV;
+            float sum = 0.f;
+            bool any = false;
+#pragma unroll
+            for (int w = 0; w < BWD_WARPS; ++w) {
+                if ((s.mask[w][jj >> 5] >> (jj & 31)) & 1u) {
+                    sum += s.acc[w][e];
+                    any = true;
+                }
+            }
+            if (any) {
+                const uint32_t id = __float_as_uint(s.B[buf][jj].w);
+                float* dst;
+                if (vi < 2) dst = dL_dmean2D + (size_t)id * 3 + vi;
+                else if (vi < 5) dst = dL_dconic2D + (size_t)id * 4 + (vi == 4 ? 3 : vi - 2);
+                else if (vi == 5) dst = dL_dopacity + id;
+                else dst = dL_dfeatures + (size_t)id * C + (vi - 6);
+                atomicAdd(dst, sum);
+            }
+        }
+    }
+}
+
+// =================================================================================================
+// host-side dispatch
+// =================================================================================================
+template <int C>
+static int launch_forward(dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
+                          const float* features, const float* bg, float* final_T, uint32_t* n_contrib,
+                          float* out_color, cudaStream_t stream) {
+    const int smem = (int)sizeof(FwdSmem<C>);
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute(blend_forward_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    blend_forward_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, features, bg, final_T, n_contrib, out_color);
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int C, int BATCH>
+static int launch_backward(dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
+                           const float* bg, const float* features, const float* final_T,
+                           const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
+                           float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream) {
+    const int smem = (int)sizeof(BwdSmem<C, BATCH>);
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_kernel<C, BATCH>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    blend_backward_kernel<C, BATCH><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
+                                                                    dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures);
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int blend_forward_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
+                           const float* features, const float* bg, float* final_T, uint32_t* n_contrib,
+                           float* out_color, cudaStream_t stream) {
+    switch (C) {
+#define R3DGW_FWD_CASE(N) case N: return launch_forward<N>(grid, ranges, A, B, W, H, features, bg, final_T, n_contrib, out_color, stream);
+        R3DGW_FWD_CASE(1) R3DGW_FWD_CASE(2) R3DGW_FWD_CASE(3) R3DGW_FWD_CASE(4) R3DGW_FWD_CASE(6)
+        R3DGW_FWD_CASE(8) R3DGW_FWD_CASE(9) R3DGW_FWD_CASE(12) R3DGW_FWD_CASE(15) R3DGW_FWD_CASE(16)
+        R3DGW_FWD_CASE(18) R3DGW_FWD_CASE(24) R3DGW_FWD_CASE(27) R3DGW_FWD_CASE(32)
+#undef R3DGW_FWD_CASE
+        default: return R3DGW_ERR_UNSUPPORTED;
+    }
+}
+
+int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
+                            const float* bg, const float* features, const float* final_T,
+                            const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
+                            float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream) {
+    switch (C) {
+#define R3DGW_BWD_CASE(N, BT) case N: return launch_backward<N, BT>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures, stream);
+        R3DGW_BWD_CASE(1, 128) R3DGW_BWD_CASE(2, 128) R3DGW_BWD_CASE(3, 128) R3DGW_BWD_CASE(4, 128)
+        R3DGW_BWD_CASE(6, 128) R3DGW_BWD_CASE(8, 64) R3DGW_BWD_CASE(9, 64) R3DGW_BWD_CASE(12, 64)
+        R3DGW_BWD_CASE(15, 64) R3DGW_BWD_CASE(16, 64) R3DGW_BWD_CASE(18, 32) R3DGW_BWD_CASE(24, 32)
+        R3DGW_BWD_CASE(27, 32) R3DGW_BWD_CASE(32, 32)
+#undef R3DGW_BWD_CASE
+        default: return R3DGW_ERR_UNSUPPORTED;
+    }
+}
+
+}  // namespace r3dgw

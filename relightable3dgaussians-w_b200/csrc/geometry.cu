@@ -1,0 +1,503 @@
+// geometry.cu - per-Gaussian stages of the splat pipeline for sm_100a:
+//   K1  preprocess_scan_kernel : cull, project, cov3D -> conic, radius, tile rect, FUSED with the
+//                                prefix sum of tiles_touched (decoupled look-back), so the separate
+//                                scan pass of the reference (rasterizer_impl.cu:276) disappears.
+//   K2  duplicate_keys_kernel  : (tile|depth) keys, warp-cooperative for large rects.
+//   K3  ranges_gather_kernel   : tile ranges + gather of the sorted-order splat stream.
+//   K8  mark_visible_kernel
+//   K6+K7 geometry_backward_kernel (fused).
+// Reference behaviour: cuda_rasterizer/forward.cu:74-256, rasterizer_impl.cu:54-138,
+// backward.cu:144-396.  Arithmetic order of the decision path mirrors the reference so that
+// radii / tiles_touched / keys are bit-identical.
+#include "common.cuh"
+#include "sh.cuh"
+
+namespace r3dgw {
+
+// ---------------------------------------------------------------------------------------------
+// cov3D from scale + (un-normalised) quaternion.  reference: computeCov3D, forward.cu:118-152
+__device__ __forceinline__ void cov3d_from_scale_rot(const float3 scale, float mod, const float4 rot,
+                                                     float* cov3D) {
+    M3 S(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
+    S.c[0][0] = mod * scale.x;
+    S.c[1][1] = mod * scale.y;
+    S.c[2][2] = mod * scale.z;
+    float r = rot.x, x = rot.y, y = rot.z, z = rot.w;
+    M3 R(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+         2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+         2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+    M3 M = m3_mul(S, R);
+    M3 Sigma = m3_mul(m3_transpose(M), M);
+    cov3D[0] = Sigma.c[0][0];
+    cov3D[1] = Sigma.c[0][1];
+    cov3D[2] = Sigma.c[0][2];
+    cov3D[3] = Sigma.c[1][1];
+    cov3D[4] = Sigma.c[1][2];
+    cov3D[5] = Sigma.c[2][2];
+}
+
+// EWA projection of the 3D covariance.  reference: computeCov2D, forward.cu:74-113
+__device__ __forceinline__ float3 cov2d_project(const float3& mean, float focal_x, float focal_y,
+                                                float tan_fovx, float tan_fovy, const float* cov3D,
+                                                const float* viewmatrix) {
+    float3 t = xform_4x3(mean, viewmatrix);
+    const float limx = 1.3f * tan_fovx;
+    const float limy = 1.3f * tan_fovy;
+    const float txtz = t.x / t.z;
+    const float tytz = t.y / t.z;
+    t.x = min(limx, max(-limx, txtz)) * t.z;
+    t.y = min(limy, max(-limy, tytz)) * t.z;
+
+    M3 J(focal_x / t.z, 0.0f, -(focal_x * t.x) / (t.z * t.z),
+         0.0f, focal_y / t.z, -(focal_y * t.y) / (t.z * t.z),
+         0, 0, 0);
+    M3 W(viewmatrix[0], viewmatrix[4], viewmatrix[8],
+         viewmatrix[1], viewmatrix[5], viewmatrix[9],
+         viewmatrix[2], viewmatrix[6], viewmatrix[10]);
+    M3 T = m3_mul(W, J);
+    M3 Vrk(cov3D[0], cov3D[1], cov3D[2],
+           cov3D[1], cov3D[3], cov3D[4],
+           cov3D[2], cov3D[4], cov3D[5]);
+    M3 cov = m3_mul(m3_mul(m3_transpose(T), m3_transpose(Vrk)), T);
+    cov.c[0][0] += 0.3f;
+    cov.c[1][1] += 0.3f;
+    return {float(cov.c[0][0]), float(cov.c[0][1]), float(cov.c[1][1])};
+}
+
+// ---------------------------------------------------------------------------------------------
+// Decoupled look-back tile state: high 32 bits flag (0 none, 1 aggregate, 2 inclusive), low 32 value.
+__device__ __forceinline__ void scan_state_store(unsigned long long* p, unsigned flag, unsigned v) {
+    unsigned long long w = ((unsigned long long)flag << 32) | v;
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ unsigned long long scan_state_load(const unsigned long long* p) {
+    unsigned long long w;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    return w;
+}
+
+struct PreprocessParams {
+    int P, D, M;
+    int W, H;
+    float tan_fovx, tan_fovy, focal_x, focal_y, scale_modifier;
+    int prefiltered;
+    unsigned grid_x, grid_y;
+    const float* means3D;
+    const float* scales;
+    const float* rotations;
+    const float* opacities;
+    const float* shs;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    int* radii;
+    float2* means2D;
+    float* depths;
+    float* cov3Ds;
+    float* rgb;
+    unsigned char* clamped;
+    float4* conic_opacity;
+    uint32_t* tiles_touched;
+    uint32_t* point_offsets;
+    unsigned long long* scan_state;
+    uint32_t* total_out;   // device scalar: R
+};
+
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_scan_kernel(const PreprocessParams p) {
+    __shared__ float s_view[16], s_proj[16];
+    __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
+    __shared__ uint32_t s_block_prefix;
+    if (threadIdx.x < 16) {
+        s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
+        s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
+    }
+    __syncthreads();
+
+    const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
+    uint32_t touched = 0;
+    if (idx < p.P) {
+        int my_radius_i = 0;
+        // reference: in_frustum (auxiliary.h:139-164): near-plane cull on view-space z only
+        float3 p_orig = {p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]};
+        float3 p_view = xform_4x3(p_orig, s_view);
+        if (p_view.z > 0.2f) {
+            float4 p_hom = xform_4x4(p_orig, s_proj);
+            float p_w = 1.0f / (p_hom.w + 0.0000001f);
+            float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+            const float* cov3D;
+            if (p.cov3D_precomp != nullptr) {
+                cov3D = p.cov3D_precomp + idx * 6;
+            } else {
+                float3 sc = {p.scales[3 * idx], p.scales[3 * idx + 1], p.scales[3 * idx + 2]};
+                float4 rq = reinterpret_cast<const float4*>(p.rotations)[idx];
+                cov3d_from_scale_rot(sc, p.scale_modifier, rq, p.cov3Ds + idx * 6);
+                cov3D = p.cov3Ds + idx * 6;
+            }
+            float3 cov = cov2d_project(p_orig, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, cov3D, s_view);
+            float det = (cov.x * cov.z - cov.y * cov.y);
+            if (det != 0.0f) {
+                float det_inv = 1.f / det;
+                float3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+                float mid = 0.5f * (cov.x + cov.z);
+                float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
+                float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
+                float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+                float2 point_image = {ndc_to_pix(p_proj.x, p.W), ndc_to_pix(p_proj.y, p.H)};
+                uint2 rmin, rmax;
+                tile_rect(point_image, my_radius, rmin, rmax, p.grid_x, p.grid_y);
+                uint32_t n = (rmax.x - rmin.x) * (rmax.y - rmin.y);
+                if (n != 0) {
+                    if (p.shs != nullptr) {
+                        float3 c = sh_to_rgb_fwd(idx, p.D, p.M, p.means3D, p.cam_pos, p.shs, p.clamped);
+                        p.rgb[idx * 3 + 0] = c.x;
+                        p.rgb[idx * 3 + 1] = c.y;
+                        p.rgb[idx * 3 + 2] = c.z;
+                    }
+                    p.depths[idx] = p_view.z;
+                    my_radius_i = my_radius;
+                    p.means2D[idx] = point_image;
+                    p.conic_opacity[idx] = {conic.x, conic.y, conic.z, p.opacities[idx]};
+                    touched = n;
+                }
+            }
+        } else if (p.prefiltered) {
+            // reference traps here (auxiliary.h:156-160)
+            __trap();
+        }
+        p.radii[idx] = my_radius_i;
+        p.tiles_touched[idx] = touched;
+    }
+
+    // ---- fused inclusive prefix sum over tiles_touched (replaces cub::DeviceScan::InclusiveSum)
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = touched;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp_sum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t ws = lane < PRE_THREADS / 32 ? s_warp_sum[lane] : 0;
+        uint32_t wi = ws;
+#pragma unroll
+        for (int o = 1; o < PRE_THREADS / 32; o <<= 1) {
+            uint32_t v = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += v;
+        }
+        if (lane < PRE_THREADS / 32) s_warp_sum[lane] = wi - ws;   // exclusive warp offsets
+        uint32_t block_total = __shfl_sync(0xffffffffu, wi, PRE_THREADS / 32 - 1);
+        // publish aggregate, look back
+        uint32_t excl = 0;
+        if (blockIdx.x == 0) {
+            if (lane == 0) scan_state_store(p.scan_state, 2u, block_total);
+        } else {
+            if (lane == 0) scan_state_store(p.scan_state + blockIdx.x, 1u, block_total);
+            int base = (int)blockIdx.x - 1;
+            while (true) {
+                int j = base - (int)lane;
+                unsigned long long w = 0;
+                unsigned flag = 2;  // virtual predecessor before block 0: inclusive 0
+                if (j >= 0) {
+                    do { w = scan_state_load(p.scan_state + j); flag = (unsigned)(w >> 32); } while (flag == 0);
+                }
+                unsigned incl_mask = __ballot_sync(0xffffffffu, flag == 2);
+                // lanes up to and including the first inclusive one contribute
+                int first = __ffs(incl_mask) - 1;   // incl_mask non-zero once j<0 lanes exist, else may be 0
+                uint32_t v = (j >= 0 && (first < 0 || (int)lane <= first)) ? (uint32_t)w : 0u;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                excl += v;
+                if (first >= 0) break;
+                base -= 32;
+            }
+            if (lane == 0) scan_state_store(p.scan_state + blockIdx.x, 2u, excl + block_total);
+        }
+        if (lane == 0) {
+            s_block_prefix = excl;
+            if (blockIdx.x == gridDim.x - 1) *p.total_out = excl + block_total;
+        }
+    }
+    __syncthreads();
+    if (idx < p.P) p.point_offsets[idx] = s_block_prefix + s_warp_sum[warp] + incl;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2.  reference: duplicateWithKeys, rasterizer_impl.cu:70-111.  Same keys, same emission order
+// (row-major over the rect, ascending Gaussian index through point_offsets); rects larger than
+// DUP_SMALL tiles are written by the whole warp so that stores coalesce and the loop is balanced.
+constexpr int DUP_SMALL = 6;
+__global__ void __launch_bounds__(256) duplicate_keys_kernel(
+    int P, const float2* __restrict__ points_xy, const float* __restrict__ depths,
+    const uint32_t* __restrict__ offsets, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
+    const int* __restrict__ radii, unsigned gx, unsigned gy) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31;
+    uint32_t n = 0, off = 0, w = 0, depth_bits = 0;
+    uint2 rmin = {0, 0}, rmax = {0, 0};
+    if (idx < P) {
+        int r = radii[idx];
+        if (r > 0) {
+            off = (idx == 0) ? 0 : offsets[idx - 1];
+            tile_rect(points_xy[idx], r, rmin, rmax, gx, gy);
+            w = rmax.x - rmin.x;
+            n = w * (rmax.y - rmin.y);
+            depth_bits = __float_as_uint(depths[idx]);
+        }
+    }
+    if (n <= DUP_SMALL) {
+        uint32_t o = off;
+        for (unsigned y = rmin.y; y < rmax.y; y++)
+            for (unsigned x = rmin.x; x < rmax.x; x++) {
+                uint64_t key = y * gx + x;
+                key <<= 32;
+                key |= depth_bits;
+                keys[o] = key;
+                vals[o] = idx;
+                o++;
+            }
+    }
+    unsigned big = __ballot_sync(0xffffffffu, n > DUP_SMALL);
+    while (big) {
+        int src = __ffs(big) - 1;
+        big &= big - 1;
+        uint32_t bn = __shfl_sync(0xffffffffu, n, src);
+        uint32_t bo = __shfl_sync(0xffffffffu, off, src);
+        uint32_t bw = __shfl_sync(0xffffffffu, w, src);
+        uint32_t bx = __shfl_sync(0xffffffffu, rmin.x, src);
+        uint32_t by = __shfl_sync(0xffffffffu, rmin.y, src);
+        uint32_t bd = __shfl_sync(0xffffffffu, depth_bits, src);
+        uint32_t bi = (uint32_t)(idx - (int)lane + src);
+        for (uint32_t k = lane; k < bn; k += 32) {
+            uint32_t y = by + k / bw, x = bx + k % bw;
+            uint64_t key = y * gx + x;
+            key <<= 32;
+            key |= bd;
+            keys[bo + k] = key;
+            vals[bo + k] = bi;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3.  reference: identifyTileRanges, rasterizer_impl.cu:116-138.  Fused with the gather that
+// builds the sorted-order splat stream consumed by the blend kernels through bulk async copies:
+//   A[i] = (x, y, conic.x, conic.y)   B[i] = (conic.z, opacity, skip_threshold, id bits)
+// skip_threshold = -log(255*opacity) - 0.01: power below it can never reach alpha >= 1/255
+// (1 % safety margin), so the blend can skip the exp without changing any decision.
+__global__ void __launch_bounds__(256) ranges_gather_kernel(
+    int L, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
+    const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+    uint2* __restrict__ ranges, float4* __restrict__ splatA, float4* __restrict__ splatB) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= L) return;
+    uint64_t key = keys[idx];
+    uint32_t currtile = key >> 32;
+    if (idx == 0)
+        ranges[currtile].x = 0;
+    else {
+        uint32_t prevtile = keys[idx - 1] >> 32;
+        if (currtile != prevtile) {
+            ranges[prevtile].y = idx;
+            ranges[currtile].x = idx;
+        }
+    }
+    if (idx == L - 1) ranges[currtile].y = L;
+
+    uint32_t id = point_list[idx];
+    float2 xy = means2D[id];
+    float4 co = conic_opacity[id];
+    float thr = (co.w > 0.0f) ? (-logf(255.0f * co.w) - 0.01f) : INFINITY;
+    if (!(co.w == co.w)) thr = -INFINITY;   // NaN opacity: never skip, let the exact path decide
+    splatA[idx] = make_float4(xy.x, xy.y, co.x, co.y);
+    splatB[idx] = make_float4(co.z, co.w, thr, __uint_as_float(id));
+}
+
+// K8. reference: checkFrustum, rasterizer_impl.cu:54-66
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
+                                    const float* __restrict__ viewmatrix, uint8_t* __restrict__ present) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    float3 v = xform_4x3(p, viewmatrix);
+    present[idx] = v.z > 0.2f;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// K6 + K7 fused: one thread per visible Gaussian turns (dL_dconic, dL_dmean2D) into gradients of
+// means3D, cov3D, scale and rotation.  reference: computeCov2DCUDA backward.cu:144-274,
+// preprocessCUDA backward.cu:346-396, computeCov3D backward.cu:278-341.  The reference runs two
+// kernels and round-trips dL_dmean3D / dL_dcov3D through HBM between them.
+struct GeomBackwardParams {
+    int P, D, M;
+    float focal_x, focal_y, tan_fovx, tan_fovy, scale_modifier;
+    const float* means3D;
+    const int* radii;
+    const float* cov3Ds;          // geometry-state cov3D or cov3D_precomp
+    const float* scales;          // may be null (cov3D_precomp path)
+    const float* rotations;
+    const float* shs;             // may be null
+    const unsigned char* clamped;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    const float* dL_dmean2D;      // [P,3]
+    const float* dL_dconic;       // [P,4]
+    float* dL_dmean3D;            // [P,3]
+    float* dL_dcolor;             // [P,3] (SH path input)
+    float* dL_dcov3D;             // [P,6]
+    float* dL_dsh;
+    float* dL_dscale;             // [P,3]
+    float* dL_drot;               // [P,4]
+};
+
+__global__ void __launch_bounds__(256) geometry_backward_kernel(const GeomBackwardParams p) {
+    __shared__ float s_view[16], s_proj[16];
+    if (threadIdx.x < 16) {
+        s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
+        s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
+    }
+    __syncthreads();
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= p.P || !(p.radii[idx] > 0)) return;
+
+    const float* view = s_view;
+    const float* proj = s_proj;
+    const float3 mean = {p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]};
+    const float* cov3D = p.cov3Ds + 6 * (size_t)idx;
+    const float4 gconic4 = reinterpret_cast<const float4*>(p.dL_dconic)[idx];
+    const float gcx = gconic4.x, gcy = gconic4.y, gcz = gconic4.w;
+
+    // ---- recompute the forward projection ----------------------------------------------------
+    float3 t = xform_4x3(mean, view);
+    const float limx = 1.3f * p.tan_fovx, limy = 1.3f * p.tan_fovy;
+    const float txtz = t.x / t.z, tytz = t.y / t.z;
+    t.x = min(limx, max(-limx, txtz)) * t.z;
+    t.y = min(limy, max(-limy, tytz)) * t.z;
+    const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+    const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+    const float hx = p.focal_x, hy = p.focal_y;
+    const float j00 = hx / t.z, j02 = -(hx * t.x) / (t.z * t.z);
+    const float j11 = hy / t.z, j12 = -(hy * t.y) / (t.z * t.z);
+    // u, v: first two columns of T = W * J;  W[k][r] = view[k + 4 r]
+    float u[3], v[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        u[r] = view[0 + 4 * r] * j00 + view[2 + 4 * r] * j02;
+        v[r] = view[1 + 4 * r] * j11 + view[2 + 4 * r] * j12;
+    }
+    const float V[3][3] = {{cov3D[0], cov3D[1], cov3D[2]}, {cov3D[1], cov3D[3], cov3D[4]}, {cov3D[2], cov3D[4], cov3D[5]}};
+    float Vu[3], Vv[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        Vu[i] = V[i][0] * u[0] + V[i][1] * u[1] + V[i][2] * u[2];
+        Vv[i] = V[i][0] * v[0] + V[i][1] * v[1] + V[i][2] * v[2];
+    }
+    const float a = (u[0] * Vu[0] + u[1] * Vu[1] + u[2] * Vu[2]) + 0.3f;
+    const float b = u[0] * Vv[0] + u[1] * Vv[1] + u[2] * Vv[2];
+    const float c = (v[0] * Vv[0] + v[1] * Vv[1] + v[2] * Vv[2]) + 0.3f;
+
+    const float denom = a * c - b * b;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    float gcov[6] = {0, 0, 0, 0, 0, 0};
+    if (denom2inv != 0) {
+        dL_da = denom2inv * (-c * c * gcx + 2 * b * c * gcy + (denom - a * c) * gcz);
+        dL_dc = denom2inv * (-a * a * gcz + 2 * a * b * gcy + (denom - a * c) * gcx);
+        dL_db = denom2inv * 2 * (b * c * gcx - (denom + 2 * b * b) * gcy + a * b * gcz);
+        // a = u'Vu, b = u'Vv, c = v'Vv  (off-diagonal entries appear twice)
+        gcov[0] = u[0] * u[0] * dL_da + u[0] * v[0] * dL_db + v[0] * v[0] * dL_dc;
+        gcov[3] = u[1] * u[1] * dL_da + u[1] * v[1] * dL_db + v[1] * v[1] * dL_dc;
+        gcov[5] = u[2] * u[2] * dL_da + u[2] * v[2] * dL_db + v[2] * v[2] * dL_dc;
+        gcov[1] = 2 * u[0] * u[1] * dL_da + (u[0] * v[1] + u[1] * v[0]) * dL_db + 2 * v[0] * v[1] * dL_dc;
+        gcov[2] = 2 * u[0] * u[2] * dL_da + (u[0] * v[2] + u[2] * v[0]) * dL_db + 2 * v[0] * v[2] * dL_dc;
+        gcov[4] = 2 * u[2] * u[1] * dL_da + (u[1] * v[2] + u[2] * v[1]) * dL_db + 2 * v[1] * v[2] * dL_dc;
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = gcov[i];
+
+    float gu[3], gv[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        gu[i] = 2 * Vu[i] * dL_da + Vv[i] * dL_db;
+        gv[i] = 2 * Vv[i] * dL_dc + Vu[i] * dL_db;
+    }
+    const float dL_dJ00 = view[0] * gu[0] + view[4] * gu[1] + view[8] * gu[2];
+    const float dL_dJ02 = view[2] * gu[0] + view[6] * gu[1] + view[10] * gu[2];
+    const float dL_dJ11 = view[1] * gv[0] + view[5] * gv[1] + view[9] * gv[2];
+    const float dL_dJ12 = view[2] * gv[0] + view[6] * gv[1] + view[10] * gv[2];
+    const float tz = 1.f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
+    const float dL_dtx = x_grad_mul * -hx * tz2 * dL_dJ02;
+    const float dL_dty = y_grad_mul * -hy * tz2 * dL_dJ12;
+    const float dL_dtz = -hx * tz2 * dL_dJ00 - hy * tz2 * dL_dJ11 + (2 * hx * t.x) * tz3 * dL_dJ02 + (2 * hy * t.y) * tz3 * dL_dJ12;
+    float3 gmean = {view[0] * dL_dtx + view[1] * dL_dty + view[2] * dL_dtz,
+                    view[4] * dL_dtx + view[5] * dL_dty + view[6] * dL_dtz,
+                    view[8] * dL_dtx + view[9] * dL_dty + view[10] * dL_dtz};
+
+    // ---- screen-space mean gradient through the projection (backward.cu:366-387) --------------
+    {
+        float4 m_hom = xform_4x4(mean, proj);
+        float m_w = 1.0f / (m_hom.w + 0.0000001f);
+        float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+        float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+        float gx = p.dL_dmean2D[3 * (size_t)idx], gy = p.dL_dmean2D[3 * (size_t)idx + 1];
+        gmean.x += (proj[0] * m_w - proj[3] * mul1) * gx + (proj[1] * m_w - proj[3] * mul2) * gy;
+        gmean.y += (proj[4] * m_w - proj[7] * mul1) * gx + (proj[5] * m_w - proj[7] * mul2) * gy;
+        gmean.z += (proj[8] * m_w - proj[11] * mul1) * gx + (proj[9] * m_w - proj[11] * mul2) * gy;
+    }
+    if (p.shs != nullptr) {
+        float3 g = sh_to_rgb_bwd(idx, p.D, p.M, p.means3D, p.cam_pos, p.shs, p.clamped, p.dL_dcolor, p.dL_dsh);
+        gmean.x += g.x; gmean.y += g.y; gmean.z += g.z;
+    }
+    p.dL_dmean3D[3 * (size_t)idx + 0] = gmean.x;
+    p.dL_dmean3D[3 * (size_t)idx + 1] = gmean.y;
+    p.dL_dmean3D[3 * (size_t)idx + 2] = gmean.z;
+
+    // ---- cov3D -> scale / rotation (backward.cu:278-341) ---------------------------------------
+    if (p.scales != nullptr) {
+        const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
+        const float r = q.x, x = q.y, y = q.z, z = q.w;
+        M3 R(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+             2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+             2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+        const float s[3] = {p.scale_modifier * p.scales[3 * idx], p.scale_modifier * p.scales[3 * idx + 1],
+                            p.scale_modifier * p.scales[3 * idx + 2]};
+        M3 Mm;   // M = S * R  ->  M[c][r] = s_r * R[c][r]
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc)
+#pragma unroll
+            for (int rr = 0; rr < 3; ++rr) Mm.c[cc][rr] = s[rr] * R.c[cc][rr];
+        M3 gS(gcov[0], 0.5f * gcov[1], 0.5f * gcov[2],
+              0.5f * gcov[1], gcov[3], 0.5f * gcov[4],
+              0.5f * gcov[2], 0.5f * gcov[4], gcov[5]);
+        M3 gM = m3_mul(Mm, gS);
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc)
+#pragma unroll
+            for (int rr = 0; rr < 3; ++rr) gM.c[cc][rr] *= 2.0f;
+        // gMt[i][j] = gM[j][i];  dL_dscale_i = sum_j R[j][i] * gM[j][i]
+        float gs[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) gs[i] = R.c[0][i] * gM.c[0][i] + R.c[1][i] * gM.c[1][i] + R.c[2][i] * gM.c[2][i];
+        p.dL_dscale[3 * (size_t)idx + 0] = gs[0];
+        p.dL_dscale[3 * (size_t)idx + 1] = gs[1];
+        p.dL_dscale[3 * (size_t)idx + 2] = gs[2];
+        // A[i][j] = dL_dMt[i][j] * s_i   with dL_dMt[i][j] = gM[j][i]
+        float A[3][3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) A[i][j] = gM.c[j][i] * s[i];
+        float4 gq;
+        gq.x = 2 * z * (A[0][1] - A[1][0]) + 2 * y * (A[2][0] - A[0][2]) + 2 * x * (A[1][2] - A[2][1]);
+        gq.y = 2 * y * (A[1][0] + A[0][1]) + 2 * z * (A[2][0] + A[0][2]) + 2 * r * (A[1][2] - A[2][1]) - 4 * x * (A[2][2] + A[1][1]);
+        gq.z = 2 * x * (A[1][0] + A[0][1]) + 2 * r * (A[2][0] - A[0][2]) + 2 * z * (A[1][2] + A[2][1]) - 4 * y * (A[2][2] + A[0][0]);
+        gq.w = 2 * r * (A[0][1] - A[1][0]) + 2 * x * (A[2][0] + A[0][2]) + 2 * y * (A[1][2] + A[2][1]) - 4 * z * (A[1][1] + A[0][0]);
+        reinterpret_cast<float4*>(p.dL_drot)[idx] = gq;
+    }
+}
+
+}  // namespace r3dgw

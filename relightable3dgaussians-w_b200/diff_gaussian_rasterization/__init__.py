@@ -1,0 +1,388 @@
+"""Drop-in `diff_gaussian_rasterization` backed by the B200-native C-ABI library.
+
+Public surface mirrors the reference binding
+(submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py):
+  GaussianRasterizationSettings (:133-144)  - same 11 fields, same order
+  GaussianRasterizer(nn.Module)  (:146-195)  - forward kwargs, error strings, markVisible
+  rasterize_gaussians(...)       (:17-38)    - positional order, returns (color[3,H,W], radii[P] int32)
+Gradients come back for (means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+cov3Ds_precomp) exactly as in :119-129.
+
+What is different underneath (B200-first, invisible to the caller):
+  * the pipeline is split into a GEOMETRY node (preprocess + sort + ranges, K1..K3) and a BLEND node
+    (K4/K5).  The reference's render() calls the rasterizer 6x per frame with identical geometry
+    (gaussian_renderer/__init__.py:160-264); here calls #2..#6 hit a one-entry geometry cache and run
+    only the blend.  In backward, autograd sums the screen-space gradients of all blend nodes and the
+    geometry backward (K6+K7) runs once - mathematically the same sum the reference accumulates into
+    the shared leaves.
+  * no torch C++ extension: tensors cross the boundary as raw device pointers + the current stream.
+Set R3DGW_GEOMETRY_CACHE=0 to run the full pipeline on every call (reference-shaped behaviour).
+"""
+import ctypes
+import os
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from r3dgw_b200 import native as _nat
+
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
+           "rasterize_gaussians_features", "clear_geometry_cache", "last_geometry_state"]
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+
+
+def _ptr(t):
+    """Device pointer or NULL for an absent (empty) tensor - the reference treats numel()==0 as absent."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32c(t, device):
+    if t is None or t.numel() == 0:
+        return None
+    if t.device != device:
+        t = t.to(device)
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+class _Holder:
+    """Allocation-callback target: the library asks for bytes, torch owns them."""
+
+    def __init__(self, device):
+        self.device = device
+        self.t = None
+
+        def _cb(_ctx, nbytes):
+            try:
+                self.t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
+                return self.t.data_ptr()
+            except Exception:   # noqa: BLE001 - surfaces as R3DGW_ERR_ALLOC
+                return 0
+
+        self.cb = _nat.ALLOC_FN(_cb)
+
+
+class GeometryState:
+    """Result of K1..K3 for one (Gaussians, camera) pair; opaque buffers + their layouts."""
+
+    def __init__(self):
+        self.P = 0
+        self.R = 0
+        self.W = 0
+        self.H = 0
+        self.has_sh = False
+        self.geom = None
+        self.binning = None
+        self.radii = None
+        self.cam = None
+        self.keep = None          # tensors whose storage the camera struct points to
+        self.handles = None       # autograd handles (h_mean2D, h_conic, h_opacity, h_rgb)
+
+    # ---- views into the opaque buffers (tests / tooling) -------------------------------------
+    def _geom_layout(self):
+        L = _nat.GeomLayout()
+        _nat.check(_nat.lib().r3dgw_get_geom_layout(self.P, int(self.has_sh), ctypes.byref(L)), "geom layout")
+        return L
+
+    def _binning_layout(self):
+        L = _nat.BinningLayout()
+        _nat.check(_nat.lib().r3dgw_get_binning_layout(self.R, self.W, self.H, ctypes.byref(L)), "binning layout")
+        return L
+
+    def _view(self, buf, off, count, dtype):
+        nbytes = count * torch.empty(0, dtype=dtype).element_size()
+        return buf[off:off + nbytes].view(dtype)
+
+    def intermediates(self):
+        GL, BL = self._geom_layout(), self._binning_layout()
+        P, R = self.P, self.R
+        tiles = ((self.W + 15) // 16) * ((self.H + 15) // 16)
+        out = {
+            "depths": self._view(self.geom, GL.depths, P, torch.float32),
+            "means2D": self._view(self.geom, GL.means2D, 2 * P, torch.float32).view(P, 2),
+            "conic_opacity": self._view(self.geom, GL.conic_opacity, 4 * P, torch.float32).view(P, 4),
+            "cov3D": self._view(self.geom, GL.cov3D, 6 * P, torch.float32).view(P, 6),
+            "tiles_touched": self._view(self.geom, GL.tiles_touched, P, torch.int32),
+            "point_offsets": self._view(self.geom, GL.point_offsets, P, torch.int32),
+            "point_list": self._view(self.binning, BL.point_list, R, torch.int32),
+            "point_list_keys": self._view(self.binning, BL.point_list_keys, R, torch.int64),
+            "ranges": self._view(self.binning, BL.ranges, 2 * tiles, torch.int32).view(tiles, 2),
+            "radii": self.radii,
+        }
+        return out
+
+
+def _make_camera(s: GaussianRasterizationSettings, device):
+    view = _f32c(s.viewmatrix, device)
+    proj = _f32c(s.projmatrix, device)
+    campos = _f32c(s.campos, device)
+    cam = _nat.Camera(int(s.image_width), int(s.image_height), float(s.tanfovx), float(s.tanfovy),
+                      float(s.scale_modifier), int(bool(s.prefiltered)),
+                      view.data_ptr(), proj.data_ptr(), campos.data_ptr())
+    return cam, (view, proj, campos)
+
+
+def _run_geometry(means3D, opacities, scales, rotations, cov3D_precomp, sh, settings):
+    device = means3D.device
+    if device.type != "cuda":
+        raise RuntimeError("diff_gaussian_rasterization (B200-native): tensors must live on a CUDA device; "
+                           "there is no CPU path")
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    L = _nat.lib()
+    st = GeometryState()
+    st.P = int(means3D.size(0))
+    st.W, st.H = int(settings.image_width), int(settings.image_height)
+    m3 = _f32c(means3D, device)
+    op = _f32c(opacities, device)
+    sc = _f32c(scales, device)
+    ro = _f32c(rotations, device)
+    cv = _f32c(cov3D_precomp, device)
+    shc = _f32c(sh, device)
+    st.has_sh = shc is not None
+    M = int(shc.size(1)) if shc is not None else 0
+    cam, keep = _make_camera(settings, device)
+    st.cam, st.keep = cam, keep
+    st.radii = torch.zeros(st.P, dtype=torch.int32, device=device)
+    gh, bh = _Holder(device), _Holder(device)
+    R = ctypes.c_int(0)
+    with torch.cuda.device(device):
+        rc = L.r3dgw_geometry_forward(gh.cb, None, bh.cb, None, st.P, int(settings.sh_degree), M,
+                                      ctypes.byref(cam), _ptr(m3), _ptr(shc), _ptr(op), _ptr(sc), _ptr(ro),
+                                      _ptr(cv), st.radii.data_ptr(), ctypes.byref(R), _stream())
+    _nat.check(rc, "r3dgw_geometry_forward")
+    st.R = int(R.value)
+    st.geom, st.binning = gh.t, bh.t
+    st.inputs = (m3, op, sc, ro, cv, shc)
+    st.sh_degree, st.M = int(settings.sh_degree), M
+    return st
+
+
+class _GeometryFn(torch.autograd.Function):
+    """K1..K3 forward; K6+K7 backward.  Outputs are zero-storage handles that only carry gradients."""
+
+    @staticmethod
+    def forward(ctx, means3D, opacities, scales, rotations, cov3D_precomp, sh, settings, box):
+        st = _run_geometry(means3D, opacities, scales, rotations, cov3D_precomp, sh, settings)
+        box.append(st)
+        ctx.st = st
+        ctx.shapes = (means3D.shape, opacities.shape, scales.shape, rotations.shape, cov3D_precomp.shape, sh.shape)
+        P, dev = st.P, means3D.device
+        z = torch.zeros(1, device=dev)
+        h_mean2D, h_conic, h_opacity, h_rgb = (z.expand(P, 3), z.expand(P, 4), z.expand(P, 1), z.expand(P, 3))
+        ctx.mark_non_differentiable(st.radii)
+        return h_mean2D, h_conic, h_opacity, h_rgb, st.radii
+
+    @staticmethod
+    def backward(ctx, g_mean2D, g_conic, g_opacity, g_rgb, _g_radii):
+        st = ctx.st
+        m3, op, sc, ro, cv, shc = st.inputs
+        P, dev = st.P, m3.device
+        L = _nat.lib()
+        g_mean2D = g_mean2D.contiguous()
+        g_conic = g_conic.contiguous()
+        flat = torch.zeros(P * (3 + 6 + 3 + 4), dtype=torch.float32, device=dev)
+        dmean3D = flat[:3 * P].view(P, 3)
+        dcov3D = flat[3 * P:9 * P].view(P, 6)
+        dscale = flat[9 * P:12 * P].view(P, 3)
+        drot = flat[12 * P:16 * P].view(P, 4)
+        dsh = torch.zeros(ctx.shapes[5], dtype=torch.float32, device=dev) if shc is not None else None
+        g_rgb_c = g_rgb.contiguous() if shc is not None else None
+        with torch.cuda.device(dev):
+            rc = L.r3dgw_geometry_backward(P, st.sh_degree, st.M, ctypes.byref(st.cam), _ptr(m3), _ptr(shc),
+                                           _ptr(sc), _ptr(ro), _ptr(cv), st.radii.data_ptr(),
+                                           st.geom.data_ptr(), g_mean2D.data_ptr(), g_conic.data_ptr(),
+                                           dmean3D.data_ptr(), _ptr(g_rgb_c), dcov3D.data_ptr(), _ptr(dsh),
+                                           dscale.data_ptr(), drot.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_geometry_backward")
+        e = lambda i: torch.zeros(ctx.shapes[i], dtype=torch.float32, device=dev)   # noqa: E731
+        g_sc = dscale if sc is not None else e(2)
+        g_ro = drot if ro is not None else e(3)
+        g_cv = dcov3D if cv is not None else e(4)
+        g_sh = dsh if shc is not None else e(5)
+        return dmean3D, g_opacity.reshape(ctx.shapes[1]), g_sc, g_ro, g_cv, g_sh, None, None
+
+
+class _BlendFn(torch.autograd.Function):
+    """K4 forward / K5 backward over a cached GeometryState."""
+
+    @staticmethod
+    def forward(ctx, h_mean2D, h_conic, h_opacity, h_rgb, means2D, features, bg, st):
+        dev = st.radii.device
+        L = _nat.lib()
+        use_sh = features.numel() == 0
+        feats = None if use_sh else _f32c(features, dev)
+        C = 3 if use_sh else int(feats.size(1))
+        bgc = _f32c(bg, dev)
+        out = torch.empty(C, st.H, st.W, dtype=torch.float32, device=dev)
+        IL = _nat.ImageLayout()
+        _nat.check(L.r3dgw_get_image_layout(st.W, st.H, ctypes.byref(IL)), "image layout")
+        img = torch.empty(IL.total, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = L.r3dgw_blend_forward(st.P, st.R, C, ctypes.byref(st.cam), st.geom.data_ptr(),
+                                       st.binning.data_ptr(), img.data_ptr(), _ptr(feats), bgc.data_ptr(),
+                                       out.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_blend_forward")
+        ctx.st, ctx.C, ctx.use_sh = st, C, use_sh
+        ctx.means2D_shape = means2D.shape
+        ctx.feat_shape = features.shape
+        ctx.save_for_backward(feats if feats is not None else torch.empty(0, device=dev), bgc, img)
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        st, C = ctx.st, ctx.C
+        feats, bgc, img = ctx.saved_tensors
+        dev = grad_out.device
+        P = st.P
+        L = _nat.lib()
+        g = grad_out.contiguous()
+        if g.dtype != torch.float32:
+            g = g.float()
+        flat = torch.zeros(P * (3 + 4 + 1 + C), dtype=torch.float32, device=dev)
+        dmean2D = flat[:3 * P].view(P, 3)
+        dconic = flat[3 * P:7 * P].view(P, 4)
+        dopac = flat[7 * P:8 * P].view(P, 1)
+        dfeat = flat[8 * P:].view(P, C)
+        with torch.cuda.device(dev):
+            rc = L.r3dgw_blend_backward(P, st.R, C, ctypes.byref(st.cam), st.geom.data_ptr(),
+                                        st.binning.data_ptr(), img.data_ptr(),
+                                        None if ctx.use_sh else feats.data_ptr(), bgc.data_ptr(), g.data_ptr(),
+                                        dmean2D.data_ptr(), dconic.data_ptr(), dopac.data_ptr(),
+                                        dfeat.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_blend_backward")
+        g_means2D = dmean2D.clone() if ctx.needs_input_grad[4] else None
+        if ctx.use_sh:
+            return dmean2D, dconic, dopac, dfeat, g_means2D, torch.zeros(ctx.feat_shape, device=dev), None, None
+        return dmean2D, dconic, dopac, None, g_means2D, dfeat, None, None
+
+
+# ---- one-entry geometry cache ---------------------------------------------------------------------
+_CACHE_ENABLED = os.environ.get("R3DGW_GEOMETRY_CACHE", "1") != "0"
+_cache = {"key": None, "entry": None}
+
+
+def clear_geometry_cache():
+    _cache["key"] = None
+    _cache["entry"] = None
+
+
+def set_geometry_cache(enabled: bool):
+    global _CACHE_ENABLED
+    _CACHE_ENABLED = bool(enabled)
+    clear_geometry_cache()
+
+
+def last_geometry_state():
+    e = _cache["entry"]
+    return e[0] if e else None
+
+
+def _tkey(t):
+    if t is None or t.numel() == 0:
+        return None
+    return (t.data_ptr(), t._version, tuple(t.shape), tuple(t.stride()), t.requires_grad)
+
+
+def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s):
+    grad_mode = torch.is_grad_enabled()
+    key = (_tkey(means3D), _tkey(opacities), _tkey(scales), _tkey(rotations), _tkey(cov3Ds_precomp), _tkey(sh),
+           int(s.image_height), int(s.image_width), float(s.tanfovx), float(s.tanfovy), float(s.scale_modifier),
+           _tkey(s.viewmatrix), _tkey(s.projmatrix), _tkey(s.campos), int(s.sh_degree), bool(s.prefiltered),
+           grad_mode)
+    if _CACHE_ENABLED and _cache["key"] == key:
+        return _cache["entry"]
+    box = []
+    handles = _GeometryFn.apply(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, box)
+    st = box[0]
+    # the entry keeps the key tensors alive, so (data_ptr, _version) cannot alias new contents
+    entry = (st, handles, (means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s.viewmatrix, s.projmatrix, s.campos))
+    if _CACHE_ENABLED:
+        _cache["key"], _cache["entry"] = key, entry
+    return entry
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings):
+    st, handles, _ = _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, raster_settings)
+    h_mean2D, h_conic, h_opacity, h_rgb, radii = handles
+    color = _BlendFn.apply(h_mean2D, h_conic, h_opacity, h_rgb, means2D, colors_precomp, raster_settings.bg, st)
+    return color, radii
+
+
+def rasterize_gaussians_features(means3D, means2D, features, opacities, scales, rotations, cov3Ds_precomp,
+                                 raster_settings, bg=None):
+    """Single-pass multi-channel variant: features[P,C] -> image[C,H,W]; C in the set the
+    library instantiates (1,2,3,4,6,8,9,12,15,16,18,24,27,32)."""
+    empty = torch.empty(0, device=means3D.device)
+    st, handles, _ = _geometry(means3D, opacities, scales if scales is not None else empty,
+                               rotations if rotations is not None else empty,
+                               cov3Ds_precomp if cov3Ds_precomp is not None else empty, empty, raster_settings)
+    h_mean2D, h_conic, h_opacity, h_rgb, radii = handles
+    if bg is None:
+        bg = torch.zeros(features.size(1), device=means3D.device)
+    image = _BlendFn.apply(h_mean2D, h_conic, h_opacity, h_rgb, means2D, features, bg, st)
+    return image, radii
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        with torch.no_grad():
+            s = self.raster_settings
+            dev = positions.device
+            P = int(positions.size(0))
+            pos = _f32c(positions, dev)
+            view, proj = _f32c(s.viewmatrix, dev), _f32c(s.projmatrix, dev)
+            present = torch.zeros(P, dtype=torch.bool, device=dev)
+            if P:
+                with torch.cuda.device(dev):
+                    rc = _nat.lib().r3dgw_mark_visible(P, pos.data_ptr(), view.data_ptr(), proj.data_ptr(),
+                                                       present.data_ptr(), _stream())
+                _nat.check(rc, "r3dgw_mark_visible")
+        return present
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        if shs is None:
+            shs = torch.Tensor([])
+        if colors_precomp is None:
+            colors_precomp = torch.Tensor([])
+        if scales is None:
+            scales = torch.Tensor([])
+        if rotations is None:
+            rotations = torch.Tensor([])
+        if cov3D_precomp is None:
+            cov3D_precomp = torch.Tensor([])
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                   cov3D_precomp, raster_settings)
