@@ -325,6 +325,12 @@ def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s):
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if means3D.size(0) == 0:   # reference short-circuit: zeros, no background (rasterize_points.cu:67-80)
+        s = raster_settings
+        return (torch.zeros(3, int(s.image_height), int(s.image_width), dtype=torch.float32, device=means3D.device),
+                torch.zeros(0, dtype=torch.int32, device=means3D.device))
     st, handles, _ = _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, raster_settings)
     h_mean2D, h_conic, h_opacity, h_rgb, radii = handles
     color = _BlendFn.apply(h_mean2D, h_conic, h_opacity, h_rgb, means2D, colors_precomp, raster_settings.bg, st)
