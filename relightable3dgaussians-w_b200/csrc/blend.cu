@@ -252,8 +252,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 #pragma unroll
             for (int ch = 0; ch < C; ++ch) s.feat[buf][tid * C + ch] = f[ch];
         }
+        __syncthreads();   // features staged; previous round's flush finished -> acc / mask / other buffer free
         if (lane < (BATCH + 31) / 32) s.mask[warp][lane] = 0;
-        __syncthreads();   // features staged; previous round's flush finished -> acc / other buffer free
+        __syncwarp();
         if (tid == 0 && i + 1 < rounds) {
             const int nb = buf ^ 1;
             const int nhi = total - (i + 1) * BATCH;
