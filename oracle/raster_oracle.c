@@ -18,8 +18,16 @@
 #include <stdlib.h>
 #include <string.h>
 #include <float.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #define TILE 16
+
+/* Threads used by the loops below (1 = the scalar, deterministic order the parity tests use; bench.py's
+ * cpu_baseline / reference legs raise it to the host core count). */
+static int g_threads = 1;
+void oracle_set_threads(int n) { g_threads = n > 0 ? n : 1; }
 
 /* column-major 3x3 with glm semantics: m[col][row] */
 typedef struct { float c[3][3]; } m3;
@@ -109,6 +117,7 @@ void oracle_preprocess(int P, const float* means, const float* scales, float mod
                        uint32_t* tiles_touched) {
     const float fy = H / (2.0f * tfy), fx = W / (2.0f * tfx);
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
+#pragma omp parallel for schedule(static) num_threads(g_threads)
     for (int i = 0; i < P; ++i) {
         radii[i] = 0; tiles_touched[i] = 0;
         const float* p = means + 3 * i;
@@ -199,6 +208,7 @@ void oracle_blend_forward(int C, int W, int H, const uint32_t* ranges, const uin
                           const float* conic_opacity, const float* feat, const float* bg,
                           float* final_T, uint32_t* n_contrib, float* out) {
     const int gx = (W + TILE - 1) / TILE;
+#pragma omp parallel for schedule(dynamic, 4) num_threads(g_threads)
     for (int py = 0; py < H; ++py) for (int px = 0; px < W; ++px) {
         const int tile = (py / TILE) * gx + (px / TILE);
         const uint32_t lo = ranges[2 * tile], hi = ranges[2 * tile + 1];
@@ -225,13 +235,16 @@ void oracle_blend_forward(int C, int W, int H, const uint32_t* ranges, const uin
     }
 }
 
-/* K5: backward.cu:399-557 (sequential accumulation instead of atomics) */
+#define ACC(dst, v) do { float _v = (v); _Pragma("omp atomic") (dst) += _v; } while (0)
+/* K5: backward.cu:399-557 (sequential accumulation when single-threaded) */
 void oracle_blend_backward(int C, int W, int H, const uint32_t* ranges, const uint32_t* list, const float* means2D,
                            const float* conic_opacity, const float* feat, const float* bg, const float* final_T,
                            const uint32_t* n_contrib, const float* dL_dpix,
                            float* dL_dmean2D /*[P,3]*/, float* dL_dconic /*[P,4]*/, float* dL_dopacity, float* dL_dfeat) {
     const int gx = (W + TILE - 1) / TILE;
     const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+    /* with g_threads > 1 the += below become atomic adds in thread order (like the GPU's atomicAdd) */
+#pragma omp parallel for schedule(dynamic, 4) num_threads(g_threads)
     for (int py = 0; py < H; ++py) for (int px = 0; px < W; ++px) {
         const int tile = (py / TILE) * gx + (px / TILE);
         const uint32_t lo = ranges[2 * tile], hi = ranges[2 * tile + 1];
@@ -263,7 +276,7 @@ void oracle_blend_backward(int C, int W, int H, const uint32_t* ranges, const ui
                 accum_rec[c] = last_alpha * last_color[c] + (1.f - last_alpha) * accum_rec[c];
                 last_color[c] = col;
                 dL_dalpha += (col - accum_rec[c]) * dpx[c];
-                dL_dfeat[id * C + c] += dchannel_dcolor * dpx[c];
+                ACC(dL_dfeat[id * C + c], dchannel_dcolor * dpx[c]);
             }
             dL_dalpha *= T;
             last_alpha = alpha;
@@ -274,12 +287,12 @@ void oracle_blend_backward(int C, int W, int H, const uint32_t* ranges, const ui
             const float gdx = G * dx, gdy = G * dy;
             const float dG_ddelx = -gdx * co[0] - gdy * co[1];
             const float dG_ddely = -gdy * co[2] - gdx * co[1];
-            dL_dmean2D[3 * id] += dL_dG * dG_ddelx * ddelx_dx;
-            dL_dmean2D[3 * id + 1] += dL_dG * dG_ddely * ddely_dy;
-            dL_dconic[4 * id] += -0.5f * gdx * dx * dL_dG;
-            dL_dconic[4 * id + 1] += -0.5f * gdx * dy * dL_dG;
-            dL_dconic[4 * id + 3] += -0.5f * gdy * dy * dL_dG;
-            dL_dopacity[id] += G * dL_dalpha;
+            ACC(dL_dmean2D[3 * id], dL_dG * dG_ddelx * ddelx_dx);
+            ACC(dL_dmean2D[3 * id + 1], dL_dG * dG_ddely * ddely_dy);
+            ACC(dL_dconic[4 * id], -0.5f * gdx * dx * dL_dG);
+            ACC(dL_dconic[4 * id + 1], -0.5f * gdx * dy * dL_dG);
+            ACC(dL_dconic[4 * id + 3], -0.5f * gdy * dy * dL_dG);
+            ACC(dL_dopacity[id], G * dL_dalpha);
         }
     }
 }
@@ -290,6 +303,7 @@ void oracle_geometry_backward(int P, const float* means, const int* radii, const
                               float tfx, float tfy, const float* dL_dmean2D, const float* dL_dconic,
                               float* dL_dmean3D, float* dL_dcov3D, float* dL_dscale, float* dL_drot) {
     const float hy = H / (2.0f * tfy), hx = W / (2.0f * tfx);
+#pragma omp parallel for schedule(static) num_threads(g_threads)
     for (int i = 0; i < P; ++i) {
         if (!(radii[i] > 0)) continue;
         const float* mean = means + 3 * i;
@@ -381,6 +395,7 @@ void oracle_mark_visible(int P, const float* means, const float* view, uint8_t* 
  * an exact search, so a brute-force scan with the same distance expression and the same insertion rule
  * (updateKBest<3>) yields the same three values. */
 void oracle_knn_dist2(int P, const float* pts, float* out) {
+#pragma omp parallel for schedule(static) num_threads(g_threads)
     for (int i = 0; i < P; ++i) {
         float best[3] = { FLT_MAX, FLT_MAX, FLT_MAX };
         for (int j = 0; j < P; ++j) {
