@@ -1,0 +1,483 @@
+#!/usr/bin/env python
+"""bench.py - train iters/s of the relit Gaussian-splat hot path (BASELINE.json metric) on N B200s.
+
+A STEP is one training iteration of the path on one view per GPU, driven through the reference's call pattern
+(r3dgw_b200.render.render == gaussian_renderer/__init__.py:69-274): fused relit shading of all Gaussians, 6 raster
+forwards on identical geometry (render, diffuse, specular, depth, normal, alpha), masked-L1-style loss against a GT
+image on 5 of them, backward through 5 raster backwards + geometry backward + shading backward (the post-15 000
+regime), and - for N > 1 - an NCCL all-reduce of the Gaussian-parameter gradients (views are sharded
+over ranks; weak scaling: one view per rank per step).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload B] [--mode dropin|fused]
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for how every field is produced.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "relightable3dgaussians-w_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "train_iters_per_s_fwd+bwd_1M_gaussians_1080p"
+UNIT = "iters/s"
+LOSS_WEIGHTS = {"render": 1.0, "diffuse_color": 0.25, "specular_color": 0.25, "depth": 0.05, "normal": 0.1}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="B", help="synthetic config name (r3dgw_b200.synthetic.CONFIGS)")
+    ap.add_argument("--mode", default="dropin", choices=["dropin", "fused"],
+                    help="dropin: 6 raster calls through the reference API; fused: one 16-channel pass")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-profile", action="store_true")
+    return ap.parse_args()
+
+
+# ---- clocks -------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi sampler running DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:   # noqa: BLE001
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:   # noqa: BLE001
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); power.append(float(c[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        busy = [s for s, p in zip(sm, power) if p > 0.5 * max(power)] or sm
+        return {"sm_mhz": statistics.median(busy), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(power)}
+
+
+# ---- workload -------------------------------------------------------------------------------------------
+def build_workload(name, rank, device):
+    """Seeded synthetic scene, one camera per rank on the 10-degree arc, GT image, env / sky SH."""
+    import torch
+    from r3dgw_b200.synthetic import CONFIGS, arc_cameras, make_scene
+    sc = make_scene(name)
+    cfg = CONFIGS[name]
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    cams = arc_cameras(cfg["W"], cfg["H"], max(world, 1), centroid_z=8.0, step_deg=2.0) if world > 1 else [sc.camera]
+    cam = cams[rank].to(device)
+    g = torch.Generator().manual_seed(777 + rank)
+    gt = torch.rand(3, cfg["H"], cfg["W"], generator=g)
+    return sc, cam, gt
+
+
+def make_lut(device):
+    """Split-sum FG table: the reference's bsdf_256_256.bin is a data asset we do not copy; same shape, analytic fit."""
+    import torch
+    res = 256
+    u = (torch.arange(res, dtype=torch.float32) + 0.5) / res
+    ndv, rough = u.view(1, res).expand(res, res), u.view(res, 1).expand(res, res)
+    c0 = torch.tensor([-1.0, -0.0275, -0.572, 0.022])
+    c1 = torch.tensor([1.0, 0.0425, 1.04, -0.04])
+    r = rough.unsqueeze(-1) * c0 + c1
+    a004 = torch.minimum(r[..., 0] * r[..., 0], torch.exp2(-9.28 * ndv)) * r[..., 0] + r[..., 1]
+    return torch.stack([-1.04 * a004 + r[..., 2], 1.04 * a004 + r[..., 3]], dim=-1).unsqueeze(0).contiguous().to(device)
+
+
+class Stepper:
+    """One training iteration of the path for either arm (same loss, same call pattern)."""
+
+    def __init__(self, impl, mode, sc, cam, device):
+        import torch
+        from r3dgw_b200 import render as R
+        self.torch, self.R = torch, R
+        self.impl, self.mode, self.cam, self.device = impl, mode, cam, device
+        self.pc = R.GaussianParams.from_scene(sc.to(device), requires_grad=True)
+        self.env_sh = sc.env_sh.to(device).clone().requires_grad_(True)
+        self.sky_sh = sc.sky_sh.to(device).clone().requires_grad_(True)
+        self.bg = torch.zeros(3, device=device)
+        self.lut = make_lut(device)
+        if impl == "native":
+            import diff_gaussian_rasterization as dgr
+            self.raster = dgr
+            self.shade_fn = R.fused_shade_fn(self.lut, 4)
+        else:
+            sys.path.insert(0, os.path.join(ROOT, "oracle"))
+            import ref_loader
+            import shade_oracle as so
+            self.raster = ref_loader.load_ref_dgr()
+            lut = self.lut
+
+            def ref_shade(pc, normals, env_sh, sky_sh, cam_pos, specular, fix_sky):
+                # the reference's torch graph (light.py:131-193 + render():119-156), eager ops on the GPU
+                return so.shade_all(env_sh, 4, lut, pc.means3D, normals, pc.albedo, pc.roughness, pc.metalness,
+                                    pc.is_sky, cam_pos, sky_sh, specular, fix_sky)
+            self.shade_fn = ref_shade
+        self.params = self.pc.leaves() + [self.env_sh, self.sky_sh]
+
+    def forward(self, cam=None):
+        cam = cam or self.cam
+        if self.mode == "fused" and self.impl == "native":
+            return self.R.render_fused(cam, self.pc, self.env_sh, self.sky_sh, self.bg, self.shade_fn)
+        return self.R.render(cam, self.pc, self.env_sh, self.sky_sh, self.raster, self.bg, self.shade_fn)
+
+    def loss(self, out, gt):
+        loss = 0.0
+        for k, w in LOSS_WEIGHTS.items():
+            loss = loss + w * (out[k] - gt).abs().mean()
+        return loss
+
+    def step(self, gt, cam=None):
+        for p in self.params:
+            p.grad = None
+        out = self.forward(cam)
+        loss = self.loss(out, gt)
+        loss.backward()
+        return loss
+
+    def flat_grads(self):
+        return self.torch.cat([p.grad.reshape(-1) for p in self.params if p.grad is not None])
+
+
+# ---- timing helpers ---------------------------------------------------------------------------------------
+def l2_flush(torch, buf):
+    buf.zero_()          # 512 MiB write > 126 MB L2, outside every timed event pair
+
+
+def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None):
+    """W untimed steps, then EXACTLY K steps each bracketed by CUDA events on the current stream (L2 flushed
+    between event pairs); barrier + synchronize on both sides; returns total ms (MAX over ranks)."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for a, b in evs:
+        l2_flush(torch, flush_buf)
+        a.record()
+        fn()
+        b.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    total = sum(a.elapsed_time(b) for a, b in evs)
+    if dist is not None:
+        t = torch.tensor([total], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total = float(t.item())
+    return total
+
+
+def algorithmic_bytes(kernel, P, Pv, R, N, tiles, C, n_pass):
+    """SURVEY.md 8(d) per-unit figures x the units one launch processes (also in DESIGN.md)."""
+    table = {
+        "preprocess_scan": 44 * P + 8 * P + 52 * Pv + 8 * P,                   # K1 + fused scan (B_pre + B_scan)
+        "duplicate_keys": 20 * P + 12 * R,
+        "sort_histogram": 8 * R,
+        "sort_onesweep_pass": 24 * R,                                          # per pass: read 12 + write 12
+        "ranges_gather": 12 * R + 8 * tiles + 24 * R + 32 * R,                 # keys+ids, gather xy/conic, write stream
+        "blend_forward": (32 + 4 * C) * R + (4 * C + 8) * N,
+        "blend_backward": (32 + 4 * C) * R + (4 * C + 8) * N + (4 * C + 24) * Pv,
+        "geometry_backward": 160 * Pv,
+        "shade_forward": 80 * P,
+        "shade_backward": 100 * P,
+    }
+    return table.get(kernel)
+
+
+def cpu_baseline(workload, budget_s=20.0):
+    """The CPU port of the reference path (oracle/, OpenMP over all host cores) on a bounded sample of the workload:
+    the first P/f Gaussians at full resolution, one raster fwd+bwd (C=3) + torch-CPU shading fwd+bwd, extrapolated to
+    the full step (x f for the per-Gaussian / per-duplicate work; 6 raster forwards and 5 backwards per step, no
+    geometry reuse - the reference recomputes everything on every call)."""
+    import numpy as np
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import raster_oracle as ro
+    import shade_oracle as so
+    from r3dgw_b200.synthetic import make_scene
+    cores = os.cpu_count() or 1
+    ro.set_threads(cores)
+    torch.set_num_threads(cores)
+    sc = make_scene(workload)
+    c = sc.camera
+    f = 2 if sc.P >= 500_000 else 1
+    Ps = sc.P // f
+    a = lambda t: t[:Ps].numpy()   # noqa: E731
+    t0 = time.perf_counter()
+    fw = ro.forward(a(sc.means3D), a(sc.scales), a(sc.rotations), a(sc.opacities), a(sc.colors),
+                    c.world_view_transform.numpy(), c.full_proj_transform.numpy(), c.image_width, c.image_height,
+                    c.tanfovx, c.tanfovy, sc.bg.numpy())
+    t_fwd = time.perf_counter() - t0
+    dL = np.full((3, c.image_height, c.image_width), 1e-3, np.float32)
+    t0 = time.perf_counter()
+    ro.backward(fw, dL)
+    t_bwd = time.perf_counter() - t0
+    # shading, torch on CPU (the reference's own CPU-executable piece), on the same sample
+    fg = ~sc.is_sky[:Ps]
+    nfg = int(fg.sum())
+    leaves = [x.clone().requires_grad_(True) for x in (sc.means3D[:Ps], sc.albedo[:nfg], sc.roughness[:nfg],
+                                                       sc.metalness[:nfg], sc.env_sh, sc.sky_sh)]
+    nrm = torch.nn.functional.normalize(sc.means3D[:Ps] * -1.0 + 0.1, dim=1)
+    lut = so.synthetic_fg_lut()
+    t0 = time.perf_counter()
+    cols = so.shade_all(leaves[4], 4, lut, leaves[0], nrm, leaves[1], leaves[2], leaves[3], sc.is_sky[:Ps],
+                        c.camera_center, leaves[5], True, False)
+    sum(x.sum() for x in cols).backward()
+    t_shade = time.perf_counter() - t0
+    step_s = f * (6 * t_fwd + 5 * t_bwd + t_shade)
+    ro.set_threads(1)
+    return {"value": 1.0 / step_s, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"first {Ps} of {sc.P} Gaussians at {c.image_width}x{c.image_height}: 1 raster fwd {t_fwd:.2f}s + "
+                      f"bwd {t_bwd:.2f}s (oracle/raster_oracle.c, OpenMP) + torch-CPU shading fwd+bwd {t_shade:.2f}s; "
+                      f"extrapolated x{f} and to 6 fwd + 5 bwd per step",
+            "measured_s": round(t_fwd + t_bwd + t_shade, 3)}
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference" and rank != 0:
+        return 0                     # the reference is single-GPU: rank 0 alone runs it
+    import torch
+    if not torch.cuda.is_available():
+        if args.impl == "reference":
+            cb = cpu_baseline(args.workload)
+            print(json.dumps({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT,
+                              "n_gpus": 0, "steps": 1, "warmup": 0, "higher_is_better": True, "cpu_baseline": cb,
+                              "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                                      "d2h_bytes_per_step": 0}, "note": "no CUDA device: CPU port only"}))
+            return 0
+        raise SystemExit("bench.py: no CUDA device - the product path is CUDA only (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1 and args.impl == "native":
+        import torch.distributed as dist_mod
+        dist_mod.init_process_group("nccl", device_id=device)
+        dist = dist_mod
+
+    from r3dgw_b200 import native
+    from r3dgw_b200.synthetic import CONFIGS, Camera
+    L = native.lib() if args.impl == "native" else None
+    ref_ok = True
+    if args.impl == "reference":
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import ref_loader
+        ref_ok = ref_loader.available()
+        if not ref_ok:
+            cb = cpu_baseline(args.workload)
+            print(json.dumps({"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": 1,
+                              "steps": 1, "warmup": 0, "ms_per_step": 1e3 / cb["value"], "higher_is_better": True,
+                              "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                              "config": {"workload": args.workload}, "cpu_baseline": cb,
+                              "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0,
+                                      "d2h_bytes_per_step": 0},
+                              "note": "oracle/_ref (reference CUDA extension) not built: CPU port of the path timed"}))
+            return 0
+
+    sc, cam, gt_cpu = build_workload(args.workload, rank, device)
+    cfg = CONFIGS[args.workload]
+    W, H, P = cfg["W"], cfg["H"], cfg["P"]
+    st = Stepper(args.impl, args.mode, sc, cam, device)
+    gt = gt_cpu.to(device)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=device)
+
+    def step_resident():
+        st.step(gt)
+        if dist is not None:
+            flat = st.flat_grads()
+            dist.all_reduce(flat)          # Gaussian-parameter gradient exchange (64 B per Gaussian) over NVLink
+
+    sampler = ClockSampler(local_rank)
+    launches0 = L.r3dgw_launch_count() if L else 0
+    # warm-up happens inside timed_steps; count launches of the timed region only
+    for _ in range(args.warmup):
+        step_resident()
+    torch.cuda.synchronize()
+    launches0 = L.r3dgw_launch_count() if L else 0
+    sampler.start()
+    total_ms = timed_steps(torch, step_resident, args.steps, 0, flush, dist)
+    clocks = sampler.stop()
+    gpu_launches = (L.r3dgw_launch_count() - launches0) if L else 0
+    ms_per_step = total_ms / args.steps
+    value = world * 1e3 / ms_per_step if args.impl == "native" else 1e3 / ms_per_step
+
+    # ---- e2e: host buffers in, loss out, through the public API ----------------------------------------
+    pin = lambda t: t.contiguous().pin_memory()   # noqa: E731
+    h_gt, h_view, h_proj = pin(gt_cpu), pin(cam.world_view_transform.cpu()), pin(cam.full_proj_transform.cpu())
+    h_cpos, h_env, h_sky = pin(cam.camera_center.cpu()), pin(sc.env_sh), pin(sc.sky_sh)
+    d_gt, d_view, d_proj = torch.empty_like(gt), torch.empty(4, 4, device=device), torch.empty(4, 4, device=device)
+    d_cpos = torch.empty(3, device=device)
+    h_loss = torch.zeros(1).pin_memory()
+    h2d = sum(t.numel() * 4 for t in (h_gt, h_view, h_proj, h_cpos, h_env, h_sky))
+
+    def step_e2e():
+        d_gt.copy_(h_gt, non_blocking=True)
+        d_view.copy_(h_view, non_blocking=True)
+        d_proj.copy_(h_proj, non_blocking=True)
+        d_cpos.copy_(h_cpos, non_blocking=True)
+        with torch.no_grad():
+            st.env_sh.copy_(h_env, non_blocking=True)
+            st.sky_sh.copy_(h_sky, non_blocking=True)
+        c = Camera(W, H, cam.FoVx, cam.FoVy, d_view, d_proj, d_cpos)
+        loss = st.step(d_gt, c)
+        if dist is not None:
+            dist.all_reduce(st.flat_grads())
+        h_loss.copy_(loss.detach().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()     # the user reads the loss every step
+
+    e2e_ms = timed_steps(torch, step_e2e, args.steps, max(3, args.warmup // 2), flush, dist) / args.steps
+    e2e_value = (world if args.impl == "native" else 1) * 1e3 / e2e_ms
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world if args.impl == "native" else 1,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {P} Gaussians, {W}x{H}, 1 view/GPU/step, shade + 6 raster fwd + "
+                                   f"5 raster bwd ({args.mode})", "l2": "512 MiB flush between timed steps",
+                       "mode": args.mode, "views_per_step": world},
+            "clocks": clocks, "gpu_launches": int(gpu_launches),
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": 4}}
+    if args.impl == "reference":
+        line["impl"] = "reference"
+        line["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
+                                "sample": "the reference has no CPU rasterizer: its UNMODIFIED CUDA extension "
+                                          "(oracle/_ref, built from /root/reference for sm_100a) + its torch shading "
+                                          "graph, same B200, same steps; CPU port figure is in the native arm's line"}
+        line["e2e"] = {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
+                       "d2h_bytes_per_step": 4}
+
+    # ---- extras: fwd-only frames/s (U3), single raster call fwd / fwd+bwd (U1) ---------------------------
+    def frame():
+        with torch.no_grad():
+            st.forward()
+    line["fps_fwd"] = (world if args.impl == "native" else 1) * 1e3 / (timed_steps(torch, frame, max(5, args.steps // 2), 2, flush, dist) / max(5, args.steps // 2))
+    s = st.raster.GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, st.bg, 1.0, cam.world_view_transform,
+                                                cam.full_proj_transform, -1, cam.camera_center, False)
+    col = sc.colors.to(device).requires_grad_(True)
+    dL = torch.full((3, H, W), 1e-3, device=device)
+    pc = st.pc
+
+    def u1(bwd):
+        if args.impl == "native":
+            st.raster.clear_geometry_cache()
+        m2 = torch.zeros_like(pc.means3D, requires_grad=True)
+        with torch.set_grad_enabled(bwd):
+            img, _ = st.raster.GaussianRasterizer(s)(means3D=pc.means3D, means2D=m2, opacities=pc.opacity,
+                                                     colors_precomp=col, scales=pc.scales, rotations=pc.rotations)
+        if bwd:
+            img.backward(dL)
+    n1 = max(5, args.steps // 2)
+    line["u1_raster_call"] = {"fwd_ms": timed_steps(torch, lambda: u1(False), n1, 2, flush, None) / n1,
+                              "fwd_bwd_ms": timed_steps(torch, lambda: u1(True), n1, 2, flush, None) / n1}
+
+    # ---- per-kernel attribution + roofline of the dominant kernel (native arm) ---------------------------
+    if args.impl == "native" and not args.no_profile:
+        import diff_gaussian_rasterization as dgr
+        st.step(gt)
+        gs = dgr.last_geometry_state()
+        Rn, Pv = int(gs.R), int((gs.radii > 0).sum().item())
+        N, tiles = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+        n_pass = (32 + int(tiles).bit_length() + 7) // 8
+        C = 16 if args.mode == "fused" else 3
+        torch.cuda.synchronize()
+        native.profile_read(reset=True)
+        native.profile_enable(True)
+        nprof = max(3, min(args.steps, 10))
+        for _ in range(nprof):
+            l2_flush(torch, flush)
+            st.step(gt)
+        torch.cuda.synchronize()
+        prof = native.profile_read(reset=True)
+        native.profile_enable(False)
+        step_kernel_ms = sum(ms for ms, _ in prof.values()) / nprof
+        kern = {k: {"ms_per_step": ms / nprof, "launches_per_step": n / nprof, "avg_launch_ms": ms / max(n, 1)}
+                for k, (ms, n) in prof.items() if n}
+        top = max(kern, key=lambda k: kern[k]["ms_per_step"])
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:   # noqa: BLE001
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        ab = algorithmic_bytes(top, P, Pv, Rn, N, tiles, C, n_pass)
+        ach = ab / (kern[top]["avg_launch_ms"] * 1e-3) / 1e9
+        line["roofline"] = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s",
+                            "frac": ach / peak, "traffic": None,
+                            "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650",
+                            "algorithmic_bytes_per_launch": ab, "avg_launch_ms": kern[top]["avg_launch_ms"],
+                            "share_of_step_kernel_time": kern[top]["ms_per_step"] / step_kernel_ms}
+        # whole forward U1 (K1..K4, C=3) against the HBM roofline - north_star's "render fwd" figure
+        fwd_bytes = sum(algorithmic_bytes(k, P, Pv, Rn, N, tiles, 3, n_pass) * (n_pass if k == "sort_onesweep_pass" else 1)
+                        for k in ("preprocess_scan", "duplicate_keys", "sort_histogram", "sort_onesweep_pass",
+                                  "ranges_gather", "blend_forward"))
+        fwd_gbs = fwd_bytes / (line["u1_raster_call"]["fwd_ms"] * 1e-3) / 1e9
+        line["roofline_fwd_call"] = {"achieved": fwd_gbs, "peak": peak, "frac": fwd_gbs / peak, "unit": "GB/s",
+                                     "algorithmic_bytes": fwd_bytes}
+        line["kernels"] = {k: {a: round(b, 5) for a, b in v.items()} for k, v in kern.items()}
+        line["scene"] = {"P": P, "P_visible": Pv, "R": Rn, "pixels": N, "tiles": tiles, "sort_passes": n_pass}
+
+    if args.impl == "native" and rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args.workload)
+
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -93,6 +93,14 @@ const char* r3dgw_version(void);
 /* Number of kernel launches issued by this library in this process so far. */
 uint64_t r3dgw_launch_count(void);
 
+/* Optional per-kernel device timing (CUDA events recorded on the caller's stream around every launch).
+ * Off by default.  r3dgw_profile_read synchronises the recorded events, adds them to per-kernel totals and
+ * copies totals (ms) / launch counts into arrays of r3dgw_profile_kernel_count() entries. */
+void r3dgw_profile_enable(int on);
+int r3dgw_profile_kernel_count(void);
+const char* r3dgw_profile_kernel_name(int id);
+int r3dgw_profile_read(double* total_ms, uint64_t* launches, int reset);
+
 /* ---- staged pipeline ------------------------------------------------------------------------ */
 
 /* K1 preprocess (+fused prefix sum) -> D2H of num_rendered -> K2 duplicate -> onesweep radix sort

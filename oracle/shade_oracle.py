@@ -56,7 +56,7 @@ def eval_sh(deg, sh, dirs):
 
 def gauss_kernel(roughness, sh_degree):
     """utils/sh_utils.py:162-181: per-band Gauss-Weierstrass factors exp(-l(l+1) * 0.3 * roughness) -> [N, (deg+1)^2]."""
-    l_idxs = torch.arange(sh_degree + 1, dtype=torch.float32).view(1, -1)
+    l_idxs = torch.arange(sh_degree + 1, dtype=torch.float32, device=roughness.device).view(1, -1)
     per_band = torch.exp(-l_idxs * (l_idxs + 1) * (0.3 * roughness))
     cols = []
     for l in range(sh_degree + 1):
@@ -161,9 +161,9 @@ def shade_all(base, sh_degree, fg_lut, positions, normals, albedo, roughness, me
     dir_pp = safe_normalize(positions - view_pos)
     rgb, dif, spc = shade(base, sh_degree, fg_lut, positions[fg], normals[fg], albedo, view_pos[fg], roughness,
                           metalness, specular)
-    colors = torch.zeros(P, 3, dtype=positions.dtype)
-    diffuse = torch.zeros(P, 3, dtype=positions.dtype)
-    spec = torch.zeros(P, 3, dtype=positions.dtype)
+    colors = torch.zeros(P, 3, dtype=positions.dtype, device=positions.device)
+    diffuse = torch.zeros(P, 3, dtype=positions.dtype, device=positions.device)
+    spec = torch.zeros(P, 3, dtype=positions.dtype, device=positions.device)
     colors[fg] = rgb
     colors[is_sky] = sky_color(sky_sh, dir_pp[is_sky], fix_sky)
     diffuse[fg] = dif

@@ -3,12 +3,44 @@
 // diff-gaussian-rasterization/cuda_rasterizer/rasterizer_impl.cu:198-433.
 #include <algorithm>
 #include <climits>
+#include <cstring>
+#include <mutex>
+#include <vector>
 #include "common.cuh"
 #include "geometry.cu"
 
 namespace r3dgw {
 
 std::atomic<uint64_t> g_launches{0};
+
+// ---- per-kernel timing registry ---------------------------------------------------------------------
+bool g_profile_on = false;
+namespace {
+struct ProfSpan { int id; cudaEvent_t e0, e1; };
+std::mutex g_prof_mu;
+std::vector<ProfSpan> g_prof_open;     // spans recorded since the last collect
+std::vector<cudaEvent_t> g_prof_pool;
+double g_prof_ms[KID_COUNT] = {0};
+uint64_t g_prof_n[KID_COUNT] = {0};
+const char* const g_prof_names[KID_COUNT] = {
+    "preprocess_scan", "duplicate_keys", "sort_histogram", "sort_scan", "sort_onesweep_pass", "ranges_gather",
+    "blend_forward", "blend_backward", "geometry_backward", "shade_forward", "shade_backward", "knn", "mark_visible"};
+cudaEvent_t prof_event() {
+    if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+}  // namespace
+void prof_mark(int id, cudaStream_t s, bool end) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (!end) {
+        ProfSpan sp{id, prof_event(), prof_event()};
+        cudaEventRecord(sp.e0, s);
+        g_prof_open.push_back(sp);
+    } else {
+        for (size_t i = g_prof_open.size(); i-- > 0;)
+            if (g_prof_open[i].id == id) { cudaEventRecord(g_prof_open[i].e1, s); break; }
+    }
+}
 
 int blend_forward_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
                            const float* features, const float* bg, float* final_T, uint32_t* n_contrib,
@@ -76,6 +108,32 @@ extern "C" {
 const char* r3dgw_version(void) { return "r3dgw_b200 0.1 sm_100a"; }
 uint64_t r3dgw_launch_count(void) { return g_launches.load(); }
 
+void r3dgw_profile_enable(int on) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_profile_on = on != 0;
+}
+int r3dgw_profile_kernel_count(void) { return KID_COUNT; }
+const char* r3dgw_profile_kernel_name(int id) { return (id >= 0 && id < KID_COUNT) ? g_prof_names[id] : ""; }
+int r3dgw_profile_read(double* total_ms, uint64_t* launches, int reset) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    for (auto& sp : g_prof_open) {
+        if (cudaEventSynchronize(sp.e1) == cudaSuccess) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, sp.e0, sp.e1) == cudaSuccess) { g_prof_ms[sp.id] += ms; g_prof_n[sp.id] += 1; }
+        }
+        g_prof_pool.push_back(sp.e0);
+        g_prof_pool.push_back(sp.e1);
+    }
+    g_prof_open.clear();
+    (void)cudaGetLastError();
+    for (int i = 0; i < KID_COUNT; ++i) {
+        if (total_ms) total_ms[i] = g_prof_ms[i];
+        if (launches) launches[i] = g_prof_n[i];
+        if (reset) { g_prof_ms[i] = 0; g_prof_n[i] = 0; }
+    }
+    return 0;
+}
+
 int r3dgw_get_geom_layout(int P, int has_sh, r3dgw_geom_layout* out) {
     if (!out || P < 0) return R3DGW_ERR_BAD_ARG;
     geom_layout(P, has_sh, out);
@@ -140,7 +198,10 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
         pp.point_offsets = (uint32_t*)(g + GL.point_offsets);
         pp.scan_state = (unsigned long long*)(g + GL.scan_state);
         pp.total_out = (uint32_t*)(g + GL.scan_state + (size_t)blocks * 8);
-        preprocess_scan_kernel<<<blocks, PRE_THREADS, 0, stream>>>(pp);
+        {
+            ProfScope ps(KID_PREPROCESS, stream);
+            preprocess_scan_kernel<<<blocks, PRE_THREADS, 0, stream>>>(pp);
+        }
         R3DGW_LAUNCH_CHECK();
         // the one blocking read-back of the path (reference: rasterizer_impl.cu:281)
         R3DGW_CUDA_TRY(cudaMemcpyAsync(&R, pp.total_out, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
@@ -168,9 +229,12 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
     uint32_t* v0 = (passes & 1) ? vals_alt : vals_main;
     uint32_t* v1 = (passes & 1) ? vals_main : vals_alt;
 
-    duplicate_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
-        P, (const float2*)(g + GL.means2D), (const float*)(g + GL.depths),
-        (const uint32_t*)(g + GL.point_offsets), k0, v0, radii, gx, gy);
+    {
+        ProfScope ps(KID_DUPLICATE, stream);
+        duplicate_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
+            P, (const float2*)(g + GL.means2D), (const float*)(g + GL.depths),
+            (const uint32_t*)(g + GL.point_offsets), k0, v0, radii, gx, gy);
+    }
     R3DGW_LAUNCH_CHECK();
 
     uint64_t* ks; uint32_t* vs;
@@ -178,9 +242,12 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
     if (rc) return rc;
     if (ks != keys_main || vs != vals_main) return R3DGW_ERR_BAD_ARG;   // internal invariant
 
-    ranges_gather_kernel<<<(R + 255) / 256, 256, 0, stream>>>(
-        (int)R, keys_main, vals_main, (const float2*)(g + GL.means2D), (const float4*)(g + GL.conic_opacity),
-        (uint2*)(b + BL.ranges), (float4*)(b + BL.splats), (float4*)(b + BL.splats) + R);
+    {
+        ProfScope ps(KID_RANGES, stream);
+        ranges_gather_kernel<<<(R + 255) / 256, 256, 0, stream>>>(
+            (int)R, keys_main, vals_main, (const float2*)(g + GL.means2D), (const float4*)(g + GL.conic_opacity),
+            (uint2*)(b + BL.ranges), (float4*)(b + BL.splats), (float4*)(b + BL.splats) + R);
+    }
     R3DGW_LAUNCH_CHECK();
     return 0;
 }
@@ -257,7 +324,10 @@ int r3dgw_geometry_backward(int P, int D, int M, const r3dgw_camera* cam, const 
     gp.dL_dmean2D = dL_dmean2D; gp.dL_dconic = dL_dconic; gp.dL_dmean3D = dL_dmean3D;
     gp.dL_dcolor = dL_dcolor; gp.dL_dcov3D = dL_dcov3D; gp.dL_dsh = dL_dsh;
     gp.dL_dscale = dL_dscale; gp.dL_drot = dL_drot;
-    geometry_backward_kernel<<<(P + 255) / 256, 256, 0, stream>>>(gp);
+    {
+        ProfScope ps(KID_GEOM_BWD, stream);
+        geometry_backward_kernel<<<(P + 255) / 256, 256, 0, stream>>>(gp);
+    }
     R3DGW_LAUNCH_CHECK();
     return 0;
 }

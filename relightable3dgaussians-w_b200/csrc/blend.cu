@@ -361,7 +361,10 @@ static int launch_forward(dim3 grid, const uint2* ranges, const float4* A, const
                           float* out_color, cudaStream_t stream) {
     const int smem = (int)sizeof(FwdSmem<C>);
     R3DGW_CUDA_TRY(cudaFuncSetAttribute(blend_forward_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    blend_forward_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, features, bg, final_T, n_contrib, out_color);
+    {
+        ProfScope ps(KID_BLEND_FWD, stream);
+        blend_forward_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, features, bg, final_T, n_contrib, out_color);
+    }
     R3DGW_LAUNCH_CHECK();
     return 0;
 }
@@ -373,8 +376,11 @@ static int launch_backward(dim3 grid, const uint2* ranges, const float4* A, cons
                            float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream) {
     const int smem = (int)sizeof(BwdSmem<C, BATCH>);
     R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_kernel<C, BATCH>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    blend_backward_kernel<C, BATCH><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
-                                                                    dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures);
+    {
+        ProfScope ps(KID_BLEND_BWD, stream);
+        blend_backward_kernel<C, BATCH><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
+                                                                        dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures);
+    }
     R3DGW_LAUNCH_CHECK();
     return 0;
 }

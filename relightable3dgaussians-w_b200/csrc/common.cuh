@@ -31,6 +31,20 @@ inline void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::mem
         if (_e != cudaSuccess) return (int)_e;              \
     } while (0)
 
+// ---- optional per-kernel device timing (CUDA events on the launching stream) ---------------------
+// Off by default; bench.py switches it on for a separate, untimed pass to attribute the step to kernels.
+enum KernelId {
+    KID_PREPROCESS = 0, KID_DUPLICATE, KID_SORT_HIST, KID_SORT_SCAN, KID_SORT_PASS, KID_RANGES, KID_BLEND_FWD,
+    KID_BLEND_BWD, KID_GEOM_BWD, KID_SHADE_FWD, KID_SHADE_BWD, KID_KNN, KID_MARK_VISIBLE, KID_COUNT
+};
+extern bool g_profile_on;
+void prof_mark(int id, cudaStream_t s, bool end);
+struct ProfScope {
+    int id; cudaStream_t s;
+    ProfScope(int id_, cudaStream_t s_) : id(id_), s(s_) { if (g_profile_on) prof_mark(id, s, false); }
+    ~ProfScope() { if (g_profile_on) prof_mark(id, s, true); }
+};
+
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---- 3x3 helper with GLM's storage (c[col][row]) and GLM's accumulate order -------------------

@@ -226,6 +226,7 @@ extern "C" int r3dgw_knn_dist2(int P, const float* points, float* mean_dist2, ch
     if (!points || !mean_dist2 || !ws) return R3DGW_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
     KnnLayout L = knn_layout(P);
+    ProfScope ps(KID_KNN, stream);
     const int nb = (P + KNN_BOX - 1) / KNN_BOX, ns = (nb + KNN_SUPER - 1) / KNN_SUPER;
     const int pb = std::min(1024, (P + 255) / 256);
     Aabb* scene = (Aabb*)(ws + L.scene);

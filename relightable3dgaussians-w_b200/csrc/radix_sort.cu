@@ -251,9 +251,15 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
         stream));
 
     int hb = (int)std::min<size_t>((size_t)(n + 256 * 16 - 1) / (256 * 16), (size_t)NUM_SMS * 8);
-    radix_histogram_kernel<KeyT><<<hb, 256, 0, stream>>>(keys_in, n, sp, hist);
+    {
+        ProfScope ps(KID_SORT_HIST, stream);
+        radix_histogram_kernel<KeyT><<<hb, 256, 0, stream>>>(keys_in, n, sp, hist);
+    }
     R3DGW_LAUNCH_CHECK();
-    radix_scan_kernel<<<sp.n_pass, SORT_RADIX, 0, stream>>>(hist);
+    {
+        ProfScope ps(KID_SORT_SCAN, stream);
+        radix_scan_kernel<<<sp.n_pass, SORT_RADIX, 0, stream>>>(hist);
+    }
     R3DGW_LAUNCH_CHECK();
 
     static bool attr_set = false;
@@ -264,9 +270,12 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
     KeyT* kin = keys_in; KeyT* kout = keys_alt;
     uint32_t* vin = vals_in; uint32_t* vout = vals_alt;
     for (int p = 0; p < sp.n_pass; ++p) {
-        onesweep_pass_kernel<KeyT><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
-            kin, vin, kout, vout, n, sp.shift[p], sp.mask[p], hist + p * SORT_RADIX, counters + p,
-            status + (size_t)p * status_per_pass);
+        {
+            ProfScope ps(KID_SORT_PASS, stream);
+            onesweep_pass_kernel<KeyT><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
+                kin, vin, kout, vout, n, sp.shift[p], sp.mask[p], hist + p * SORT_RADIX, counters + p,
+                status + (size_t)p * status_per_pass);
+        }
         R3DGW_LAUNCH_CHECK();
         std::swap(kin, kout);
         std::swap(vin, vout);

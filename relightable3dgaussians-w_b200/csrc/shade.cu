@@ -400,6 +400,7 @@ extern "C" int r3dgw_shade_forward(const r3dgw_shade_args* a, float* rgb, float*
     cudaStream_t stream = (cudaStream_t)stream_;
     ShadeParams p = to_params(a);
     const int blocks = (a->P + 255) / 256;
+    ProfScope ps(KID_SHADE_FWD, stream);
     switch (a->sh_degree) {
         case 2: shade_forward_kernel<2><<<blocks, 256, 0, stream>>>(p, rgb, diffuse, specular); break;
         case 3: shade_forward_kernel<3><<<blocks, 256, 0, stream>>>(p, rgb, diffuse, specular); break;
@@ -420,6 +421,7 @@ extern "C" int r3dgw_shade_backward(const r3dgw_shade_args* a, const float* dL_d
     cudaStream_t stream = (cudaStream_t)stream_;
     ShadeParams p = to_params(a);
     const int blocks = std::min((a->P + 255) / 256, NUM_SMS * 4);
+    ProfScope ps(KID_SHADE_BWD, stream);
     switch (a->sh_degree) {
         case 2: shade_backward_kernel<2><<<blocks, 256, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
         case 3: shade_backward_kernel<3><<<blocks, 256, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;

@@ -23,7 +23,8 @@ SYMBOLS = [
     "r3dgw_launch_count", "r3dgw_geometry_forward", "r3dgw_blend_forward", "r3dgw_blend_backward",
     "r3dgw_geometry_backward", "r3dgw_rasterize_forward", "r3dgw_rasterize_backward",
     "r3dgw_mark_visible", "r3dgw_knn_workspace_bytes", "r3dgw_knn_dist2", "r3dgw_shade_forward",
-    "r3dgw_shade_backward",
+    "r3dgw_shade_backward", "r3dgw_profile_enable", "r3dgw_profile_kernel_count", "r3dgw_profile_kernel_name",
+    "r3dgw_profile_read",
 ]
 
 
@@ -139,12 +140,32 @@ def lib():
     sa = ctypes.POINTER(ShadeArgs)
     L.r3dgw_shade_forward.argtypes = [sa, vp, vp, vp, vp]
     L.r3dgw_shade_backward.argtypes = [sa] + [vp] * 11
+    L.r3dgw_profile_enable.argtypes = [ci]
+    L.r3dgw_profile_enable.restype = None
+    L.r3dgw_profile_kernel_name.argtypes = [ci]
+    L.r3dgw_profile_kernel_name.restype = ctypes.c_char_p
+    L.r3dgw_profile_read.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_uint64), ci]
     for name in SYMBOLS:
         fn = getattr(L, name)
-        if name not in ("r3dgw_version", "r3dgw_launch_count", "r3dgw_knn_workspace_bytes"):
+        if name not in ("r3dgw_version", "r3dgw_launch_count", "r3dgw_knn_workspace_bytes", "r3dgw_profile_enable",
+                        "r3dgw_profile_kernel_name"):
             fn.restype = ci
     _lib = L
     return L
+
+
+def profile_enable(on=True):
+    lib().r3dgw_profile_enable(int(bool(on)))
+
+
+def profile_read(reset=True):
+    """{kernel name: (total_ms, launches)} accumulated since the last reset."""
+    L = lib()
+    n = L.r3dgw_profile_kernel_count()
+    ms = (ctypes.c_double * n)()
+    cnt = (ctypes.c_uint64 * n)()
+    L.r3dgw_profile_read(ms, cnt, int(bool(reset)))
+    return {L.r3dgw_profile_kernel_name(i).decode(): (ms[i], int(cnt[i])) for i in range(n)}
 
 
 class R3dgwError(RuntimeError):
