@@ -344,8 +344,11 @@ def main():
             dist.all_reduce(flat)          # Gaussian-parameter gradient exchange (64 B per Gaussian) over NVLink
 
     sampler = ClockSampler(local_rank)
-    launches0 = L.r3dgw_launch_count() if L else 0
-    # warm-up happens inside timed_steps; count launches of the timed region only
+    # setup (not part of W): a few iterations so that torch's caching allocator has grown its pools; the first
+    # iterations otherwise pay cudaMalloc (a device-wide sync each) inside the step
+    for _ in range(6):
+        step_resident()
+    torch.cuda.synchronize()
     for _ in range(args.warmup):
         step_resident()
     torch.cuda.synchronize()

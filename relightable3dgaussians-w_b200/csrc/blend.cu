@@ -57,6 +57,28 @@ __device__ __forceinline__ void tile_pixel(unsigned tid, unsigned& px, unsigned&
     py = (warp >> 1) * 4 + (lane >> 3);
 }
 
+// Warp-level culling: one lane tests one staged splat against the warp's 8x4 pixel footprint.
+// q(d) = A dx^2 + 2 B dx dy + C dy^2 is convex, so its minimum over the footprint's box of offsets
+// d = centre - pixel is 0 when the centre is inside and otherwise lies on one of the four edges, where it
+// is a clamped 1-D minimisation.  power = -q/2; if even the largest power in the footprint is below the
+// splat's skip threshold (B.z, see K3) every lane would skip it, so the warp never enters the per-pixel
+// loop for it.  Conservative: margins absorb rounding, and anything odd (A<=0, NaN) keeps the splat.
+__device__ __forceinline__ bool splat_may_touch(const float4 a, const float4 b, float rx0, float rx1,
+                                                float ry0, float ry1) {
+    const float x0 = a.x - rx1, x1 = a.x - rx0, y0 = a.y - ry1, y1 = a.y - ry0;
+    if (x0 <= 0.f && x1 >= 0.f && y0 <= 0.f && y1 >= 0.f) return true;
+    const float A = a.z, B = a.w, C = b.x;
+    if (!(A > 0.f) || !(C > 0.f)) return true;
+    const float nBiC = -B * __frcp_rn(C), nBiA = -B * __frcp_rn(A);
+    float t, q, qmin;
+    t = fminf(fmaxf(nBiC * x0, y0), y1); qmin = A * x0 * x0 + (2.f * B * x0 + C * t) * t;
+    t = fminf(fmaxf(nBiC * x1, y0), y1); q = A * x1 * x1 + (2.f * B * x1 + C * t) * t; qmin = fminf(qmin, q);
+    t = fminf(fmaxf(nBiA * y0, x0), x1); q = C * y0 * y0 + (2.f * B * y0 + A * t) * t; qmin = fminf(qmin, q);
+    t = fminf(fmaxf(nBiA * y1, x0), x1); q = C * y1 * y1 + (2.f * B * y1 + A * t) * t; qmin = fminf(qmin, q);
+    // keep unless the best power in the footprint is safely below the skip threshold
+    return !(-0.5f * qmin < b.z - (2e-3f + 1e-5f * qmin));
+}
+
 // =================================================================================================
 // K4 forward
 // =================================================================================================
@@ -85,6 +107,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     const float2 pixf = {(float)pix.x, (float)pix.y};
     const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
     bool done = !inside;
+    const unsigned lane = tid & 31, warp = tid >> 5;
+    const float rx0 = (float)(blockIdx.x * TILE_X + (warp & 1) * 8), rx1 = rx0 + 7.f;
+    const float ry0 = (float)(blockIdx.y * TILE_Y + (warp >> 1) * 4), ry1 = ry0 + 3.f;
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     const int total = (int)(range.y - range.x);
@@ -131,26 +156,36 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
             bulk_g2s(s.A[nb], splatA + off, ncnt * 16u, &s.bar[nb]);
             bulk_g2s(s.B[nb], splatB + off, ncnt * 16u, &s.bar[nb]);
         }
-        if (done) continue;
+        if (__all_sync(0xffffffffu, done)) continue;   // whole warp finished: only keep the barriers company
         const uint32_t base = (uint32_t)i * FWD_BATCH;
-        for (int j = 0; j < cnt; ++j) {
-            const float4 a = s.A[buf][j];
-            const float4 b = s.B[buf][j];
-            const float2 d = {a.x - pixf.x, a.y - pixf.y};
-            const float power = -0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y;
-            if (power > 0.0f) continue;
-            if (power < b.z) continue;   // cannot reach alpha >= 1/255 (conservative, see K3)
-            const float alpha = min(0.99f, b.y * exp(power));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) {
-                done = true;
-                break;
-            }
+        for (int c0 = 0; c0 < cnt; c0 += 32) {
+            const int jl = c0 + (int)lane;
+            bool keep = false;
+            if (jl < cnt) keep = splat_may_touch(s.A[buf][jl], s.B[buf][jl], rx0, rx1, ry0, ry1);
+            unsigned m = __ballot_sync(0xffffffffu, keep);
+            while (m) {
+                const int j = c0 + __ffs(m) - 1;
+                m &= m - 1;
+                if (done) continue;
+                const float4 a = s.A[buf][j];
+                const float4 b = s.B[buf][j];
+                const float2 d = {a.x - pixf.x, a.y - pixf.y};
+                const float power = -0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y;
+                if (power > 0.0f) continue;
+                if (power < b.z) continue;   // cannot reach alpha >= 1/255 (conservative, see K3)
+                const float alpha = min(0.99f, b.y * exp(power));
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) {
+                    done = true;
+                    continue;
+                }
 #pragma unroll
-            for (int ch = 0; ch < C; ++ch) Cacc[ch] += s.feat[buf][j * C + ch] * alpha * T;
-            T = test_T;
-            last_contributor = base + (uint32_t)j + 1u;
+                for (int ch = 0; ch < C; ++ch) Cacc[ch] += s.feat[buf][j * C + ch] * alpha * T;
+                T = test_T;
+                last_contributor = base + (uint32_t)j + 1u;
+            }
+            if (__all_sync(0xffffffffu, done)) break;
         }
     }
 
@@ -197,6 +232,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
     const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
+
+    const float rx0 = (float)(blockIdx.x * TILE_X + (warp & 1) * 8), rx1 = rx0 + 7.f;
+    const float ry0 = (float)(blockIdx.y * TILE_Y + (warp >> 1) * 4), ry1 = ry0 + 3.f;
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     const float T_final = inside ? final_Ts[pix_id] : 0;
@@ -266,10 +304,19 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
         }
 
         if ((uint32_t)lo < warp_last) {
-            uint32_t my_mask = 0;   // lane 0 collects contribution bits, 32 splats at a time
-            for (int jj = cnt - 1; jj >= 0; --jj) {
-                const uint32_t k = (uint32_t)(lo + jj);
-                if (k < warp_last) {
+            // 32 splats at a time, deepest first: lane-parallel footprint cull, then the survivors back to front
+            for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
+                const int jl = c0 + (int)lane;
+                bool keep = false;
+                if (jl < cnt && (uint32_t)(lo + jl) < warp_last)
+                    keep = splat_may_touch(s.A[buf][jl], s.B[buf][jl], rx0, rx1, ry0, ry1);
+                unsigned m = __ballot_sync(0xffffffffu, keep);
+                uint32_t my_mask = 0;   // bit b: splat c0+b received something from this warp
+                while (m) {
+                    const int bit = 31 - __clz(m);
+                    m &= ~(1u << bit);
+                    const int jj = c0 + bit;
+                    const uint32_t k = (uint32_t)(lo + jj);
                     const float4 a = s.A[buf][jj];
                     const float4 b = s.B[buf][jj];
                     const float2 d = {a.x - pixf.x, a.y - pixf.y};
@@ -315,13 +362,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                         }
                         float* slot = &s.acc[warp][jj * NV];
                         warp_reduce_multi<NV>(g, lane, [&](int vi, float v) { slot[vi] = v; });
-                        my_mask |= 1u << (jj & 31);
+                        my_mask |= 1u << bit;
                     }
                 }
-                if ((jj & 31) == 0) {
-                    if (lane == 0) s.mask[warp][jj >> 5] = my_mask;
-                    my_mask = 0;
-                }
+                if (lane == 0) s.mask[warp][c0 >> 5] = my_mask;
             }
         }
         __syncthreads();   // all warps' partial sums parked

