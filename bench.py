@@ -337,11 +337,13 @@ def main():
     gt = gt_cpu.to(device)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=device)
 
+    from r3dgw_b200.parallel import GradBucket
+    bucket = GradBucket(st.params) if dist is not None else None
+
     def step_resident():
         st.step(gt)
-        if dist is not None:
-            flat = st.flat_grads()
-            dist.all_reduce(flat)          # Gaussian-parameter gradient exchange (64 B per Gaussian) over NVLink
+        if bucket is not None:
+            bucket.all_reduce(average_over=world)   # gradient exchange (64 B per Gaussian) over NVLink, ONE all-reduce
 
     sampler = ClockSampler(local_rank)
     # setup (not part of W): a few iterations so that torch's caching allocator has grown its pools; the first
@@ -379,8 +381,8 @@ def main():
             st.sky_sh.copy_(h_sky, non_blocking=True)
         c = Camera(W, H, cam.FoVx, cam.FoVy, d_view, d_proj, d_cpos)
         loss = st.step(d_gt, c)
-        if dist is not None:
-            dist.all_reduce(st.flat_grads())
+        if bucket is not None:
+            bucket.all_reduce(average_over=world)
         h_loss.copy_(loss.detach().reshape(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the user reads the loss every step
 
