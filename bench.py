@@ -386,7 +386,9 @@ def main():
         h_loss.copy_(loss.detach().reshape(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the user reads the loss every step
 
-    e2e_ms = timed_steps(torch, step_e2e, args.steps, max(3, args.warmup // 2), flush, dist) / args.steps
+    for _ in range(4):          # setup: pinned-copy path and allocator pools for the e2e variant of the step
+        step_e2e()
+    e2e_ms = timed_steps(torch, step_e2e, args.steps, max(3, args.warmup), flush, dist) / args.steps
     e2e_value = (world if args.impl == "native" else 1) * 1e3 / e2e_ms
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world if args.impl == "native" else 1,
@@ -436,6 +438,20 @@ def main():
     n1 = max(5, args.steps // 2)
     line["u1_raster_call"] = {"fwd_ms": timed_steps(torch, lambda: u1(False), n1, 2, flush, None) / n1,
                               "fwd_bwd_ms": timed_steps(torch, lambda: u1(True), n1, 2, flush, None) / n1}
+
+    # ---- the single-pass alternative API (render_fused: one 16-channel K4/K5), same step otherwise ------------
+    if args.impl == "native" and args.mode == "dropin":
+        st_f = Stepper("native", "fused", sc, cam, device)
+
+        def step_fused():
+            st_f.step(gt)
+            if dist is not None:
+                dist.all_reduce(st_f.flat_grads())
+        nfz = max(5, args.steps // 2)
+        ms_f = timed_steps(torch, step_fused, nfz, 4, flush, dist) / nfz
+        line["fused_single_pass"] = {"value": world * 1e3 / ms_f, "unit": UNIT, "ms_per_step": ms_f,
+                                     "api": "r3dgw_b200.render.render_fused (SURVEY 8f N1/N2), same loss and gradients"}
+        del st_f
 
     # ---- per-kernel attribution + roofline of the dominant kernel (native arm) ---------------------------
     if args.impl == "native" and not args.no_profile:

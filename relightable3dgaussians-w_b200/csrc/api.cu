@@ -246,7 +246,7 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
         ProfScope ps(KID_RANGES, stream);
         ranges_gather_kernel<<<(R + 255) / 256, 256, 0, stream>>>(
             (int)R, keys_main, vals_main, (const float2*)(g + GL.means2D), (const float4*)(g + GL.conic_opacity),
-            (uint2*)(b + BL.ranges), (float4*)(b + BL.splats), (float4*)(b + BL.splats) + R);
+            (uint2*)(b + BL.ranges), (float4*)(b + BL.splats), (float4*)(b + BL.splats) + R, gx);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;

@@ -57,26 +57,11 @@ __device__ __forceinline__ void tile_pixel(unsigned tid, unsigned& px, unsigned&
     py = (warp >> 1) * 4 + (lane >> 3);
 }
 
-// Warp-level culling: one lane tests one staged splat against the warp's 8x4 pixel footprint.
-// q(d) = A dx^2 + 2 B dx dy + C dy^2 is convex, so its minimum over the footprint's box of offsets
-// d = centre - pixel is 0 when the centre is inside and otherwise lies on one of the four edges, where it
-// is a clamped 1-D minimisation.  power = -q/2; if even the largest power in the footprint is below the
-// splat's skip threshold (B.z, see K3) every lane would skip it, so the warp never enters the per-pixel
-// loop for it.  Conservative: margins absorb rounding, and anything odd (A<=0, NaN) keeps the splat.
-__device__ __forceinline__ bool splat_may_touch(const float4 a, const float4 b, float rx0, float rx1,
-                                                float ry0, float ry1) {
-    const float x0 = a.x - rx1, x1 = a.x - rx0, y0 = a.y - ry1, y1 = a.y - ry0;
-    if (x0 <= 0.f && x1 >= 0.f && y0 <= 0.f && y1 >= 0.f) return true;
-    const float A = a.z, B = a.w, C = b.x;
-    if (!(A > 0.f) || !(C > 0.f)) return true;
-    const float nBiC = -B * __frcp_rn(C), nBiA = -B * __frcp_rn(A);
-    float t, q, qmin;
-    t = fminf(fmaxf(nBiC * x0, y0), y1); qmin = A * x0 * x0 + (2.f * B * x0 + C * t) * t;
-    t = fminf(fmaxf(nBiC * x1, y0), y1); q = A * x1 * x1 + (2.f * B * x1 + C * t) * t; qmin = fminf(qmin, q);
-    t = fminf(fmaxf(nBiA * y0, x0), x1); q = C * y0 * y0 + (2.f * B * y0 + A * t) * t; qmin = fminf(qmin, q);
-    t = fminf(fmaxf(nBiA * y1, x0), x1); q = C * y1 * y1 + (2.f * B * y1 + A * t) * t; qmin = fminf(qmin, q);
-    // keep unless the best power in the footprint is safely below the skip threshold
-    return !(-0.5f * qmin < b.z - (2e-3f + 1e-5f * qmin));
+// Warp-level culling: K3 (geometry.cu) tested every splat of a tile list against the eight 8x4 warp footprints of
+// its tile (exact minimum of the conic quadratic over the footprint) and left the result in the low 8 mantissa bits
+// of the skip threshold B.z.  A lane reads one splat's bit, the warp ballots, and only survivors are walked.
+__device__ __forceinline__ bool splat_touches_warp(const float4 b, unsigned warp) {
+    return (__float_as_uint(b.z) >> warp) & 1u;
 }
 
 // =================================================================================================
@@ -108,8 +93,6 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
     bool done = !inside;
     const unsigned lane = tid & 31, warp = tid >> 5;
-    const float rx0 = (float)(blockIdx.x * TILE_X + (warp & 1) * 8), rx1 = rx0 + 7.f;
-    const float ry0 = (float)(blockIdx.y * TILE_Y + (warp >> 1) * 4), ry1 = ry0 + 3.f;
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     const int total = (int)(range.y - range.x);
@@ -161,7 +144,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
         for (int c0 = 0; c0 < cnt; c0 += 32) {
             const int jl = c0 + (int)lane;
             bool keep = false;
-            if (jl < cnt) keep = splat_may_touch(s.A[buf][jl], s.B[buf][jl], rx0, rx1, ry0, ry1);
+            if (jl < cnt) keep = splat_touches_warp(s.B[buf][jl], warp);
             unsigned m = __ballot_sync(0xffffffffu, keep);
             while (m) {
                 const int j = c0 + __ffs(m) - 1;
@@ -180,8 +163,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                     done = true;
                     continue;
                 }
+                const float w = alpha * T;   // (f*alpha)*T in the reference: differs by <= 1 ulp per term
 #pragma unroll
-                for (int ch = 0; ch < C; ++ch) Cacc[ch] += s.feat[buf][j * C + ch] * alpha * T;
+                for (int ch = 0; ch < C; ++ch) Cacc[ch] += s.feat[buf][j * C + ch] * w;
                 T = test_T;
                 last_contributor = base + (uint32_t)j + 1u;
             }
@@ -232,9 +216,6 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
     const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
-
-    const float rx0 = (float)(blockIdx.x * TILE_X + (warp & 1) * 8), rx1 = rx0 + 7.f;
-    const float ry0 = (float)(blockIdx.y * TILE_Y + (warp >> 1) * 4), ry1 = ry0 + 3.f;
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     const float T_final = inside ? final_Ts[pix_id] : 0;
@@ -309,7 +290,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                 const int jl = c0 + (int)lane;
                 bool keep = false;
                 if (jl < cnt && (uint32_t)(lo + jl) < warp_last)
-                    keep = splat_may_touch(s.A[buf][jl], s.B[buf][jl], rx0, rx1, ry0, ry1);
+                    keep = splat_touches_warp(s.B[buf][jl], warp);
                 unsigned m = __ballot_sync(0xffffffffu, keep);
                 uint32_t my_mask = 0;   // bit b: splat c0+b received something from this warp
                 while (m) {
@@ -333,7 +314,8 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 #pragma unroll
                         for (int q = 0; q < NV; ++q) g[q] = 0.f;
                         if (valid) {
-                            T = T / (1.f - alpha);
+                            const float inv_1ma = __frcp_rn(1.f - alpha);   // alpha <= 0.99
+                            T = T * inv_1ma;
                             const float dchannel_dcolor = alpha * T;
                             float dL_dalpha = 0.0f;
 #pragma unroll
@@ -347,7 +329,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                             }
                             dL_dalpha *= T;
                             last_alpha = alpha;
-                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                            dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
                             const float dL_dG = b.y * dL_dalpha;
                             const float gdx = G * d.x;
                             const float gdy = G * d.y;

@@ -282,15 +282,36 @@ __global__ void __launch_bounds__(256) duplicate_keys_kernel(
 }
 
 // ---------------------------------------------------------------------------------------------
+// Exact footprint test used to build the per-warp cull mask: q(d) = A dx^2 + 2 B dx dy + C dy^2 is convex, so its
+// minimum over the box of offsets d = centre - pixel of an 8x4 pixel footprint is 0 when the centre is inside and
+// otherwise lies on one of the four edges (a clamped 1-D minimisation each).  power = -q/2; if even the largest power
+// in the footprint is safely below the splat's skip threshold no pixel of that warp can use the splat.
+// Conservative: margins absorb rounding, and anything odd (A <= 0, NaN) keeps the splat.
+__device__ __forceinline__ bool splat_may_touch(float cx, float cy, float A, float B, float C, float thr, float rx0,
+                                                float rx1, float ry0, float ry1) {
+    const float x0 = cx - rx1, x1 = cx - rx0, y0 = cy - ry1, y1 = cy - ry0;
+    if (x0 <= 0.f && x1 >= 0.f && y0 <= 0.f && y1 >= 0.f) return true;
+    if (!(A > 0.f) || !(C > 0.f)) return true;
+    const float nBiC = -B / C, nBiA = -B / A;
+    float t, q, qmin;
+    t = fminf(fmaxf(nBiC * x0, y0), y1); qmin = A * x0 * x0 + (2.f * B * x0 + C * t) * t;
+    t = fminf(fmaxf(nBiC * x1, y0), y1); q = A * x1 * x1 + (2.f * B * x1 + C * t) * t; qmin = fminf(qmin, q);
+    t = fminf(fmaxf(nBiA * y0, x0), x1); q = C * y0 * y0 + (2.f * B * y0 + A * t) * t; qmin = fminf(qmin, q);
+    t = fminf(fmaxf(nBiA * y1, x0), x1); q = C * y1 * y1 + (2.f * B * y1 + A * t) * t; qmin = fminf(qmin, q);
+    return !(-0.5f * qmin < thr - (2e-3f + 1e-5f * qmin));
+}
+
 // K3.  reference: identifyTileRanges, rasterizer_impl.cu:116-138.  Fused with the gather that
 // builds the sorted-order splat stream consumed by the blend kernels through bulk async copies:
-//   A[i] = (x, y, conic.x, conic.y)   B[i] = (conic.z, opacity, skip_threshold, id bits)
+//   A[i] = (x, y, conic.x, conic.y)   B[i] = (conic.z, opacity, skip_threshold | cull mask, id bits)
 // skip_threshold = -log(255*opacity) - 0.01: power below it can never reach alpha >= 1/255
-// (1 % safety margin), so the blend can skip the exp without changing any decision.
+// (1 % safety margin), so the blend can skip the exp without changing any decision.  Its low 8 mantissa bits
+// (a perturbation < 2e-4, inside the margin) carry the cull mask: bit w set <=> the splat can reach the 8x4
+// footprint of warp w of its tile (warp w covers columns (w&1)*8.., rows (w>>1)*4.. - blend.cu tile_pixel).
 __global__ void __launch_bounds__(256) ranges_gather_kernel(
     int L, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
-    uint2* __restrict__ ranges, float4* __restrict__ splatA, float4* __restrict__ splatB) {
+    uint2* __restrict__ ranges, float4* __restrict__ splatA, float4* __restrict__ splatB, unsigned gx) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= L) return;
     uint64_t key = keys[idx];
@@ -309,10 +330,18 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(
     uint32_t id = point_list[idx];
     float2 xy = means2D[id];
     float4 co = conic_opacity[id];
-    float thr = (co.w > 0.0f) ? (-logf(255.0f * co.w) - 0.01f) : INFINITY;
-    if (!(co.w == co.w)) thr = -INFINITY;   // NaN opacity: never skip, let the exact path decide
+    float thr = (co.w > 0.0f) ? (-logf(255.0f * co.w) - 0.01f) : 1e30f;   // opacity <= 0: every power (<= 0) skips
+    if (!(co.w == co.w)) thr = -1e30f;   // NaN opacity: never skip, let the exact path decide
+    const float tx = (float)((currtile % gx) * TILE_X), ty = (float)((currtile / gx) * TILE_Y);
+    uint32_t mask = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+        const float rx0 = tx + (float)((w & 1) * 8), ry0 = ty + (float)((w >> 1) * 4);
+        if (splat_may_touch(xy.x, xy.y, co.x, co.y, co.z, thr, rx0, rx0 + 7.f, ry0, ry0 + 3.f)) mask |= 1u << w;
+    }
+    const float thr_packed = __uint_as_float((__float_as_uint(thr) & ~0xFFu) | mask);
     splatA[idx] = make_float4(xy.x, xy.y, co.x, co.y);
-    splatB[idx] = make_float4(co.z, co.w, thr, __uint_as_float(id));
+    splatB[idx] = make_float4(co.z, co.w, thr_packed, __uint_as_float(id));
 }
 
 // K8. reference: checkFrustum, rasterizer_impl.cu:54-66
