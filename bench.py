@@ -61,7 +61,7 @@ class ClockSampler:
     def start(self):
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except Exception:   # noqa: BLE001
             self.p = None
@@ -351,11 +351,11 @@ def main():
     for _ in range(6):
         step_resident()
     torch.cuda.synchronize()
+    sampler.start()                 # started before the warm-up so nvidia-smi's own start-up is over by the timed region
     for _ in range(args.warmup):
         step_resident()
     torch.cuda.synchronize()
     launches0 = L.r3dgw_launch_count() if L else 0
-    sampler.start()
     total_ms = timed_steps(torch, step_resident, args.steps, 0, flush, dist)
     clocks = sampler.stop()
     gpu_launches = (L.r3dgw_launch_count() - launches0) if L else 0

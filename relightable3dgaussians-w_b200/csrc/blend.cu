@@ -314,8 +314,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 #pragma unroll
                         for (int q = 0; q < NV; ++q) g[q] = 0.f;
                         if (valid) {
-                            const float inv_1ma = __frcp_rn(1.f - alpha);   // alpha <= 0.99
-                            T = T * inv_1ma;
+                            T = T / (1.f - alpha);   // same expression as the reference: per-pixel terms stay bit-identical
                             const float dchannel_dcolor = alpha * T;
                             float dL_dalpha = 0.0f;
 #pragma unroll
@@ -329,7 +328,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                             }
                             dL_dalpha *= T;
                             last_alpha = alpha;
-                            dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
+                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
                             const float dL_dG = b.y * dL_dalpha;
                             const float gdx = G * d.x;
                             const float gdy = G * d.y;

@@ -21,22 +21,24 @@ def _settings(mod, sc, bg=None):
         projmatrix=cam.full_proj_transform, sh_degree=-1, campos=cam.camera_center, prefiltered=False)
 
 
-def _grad_close(a, b, name):
+def _grad_close(a, b, name, b2=None):
     """north_star: <= 1e-3 relative on gradients (atomic order differs).  The reference's own atomicAdd order makes
-    ITS gradients differ run to run: measured ref-vs-ref on B200 (profiles/r01_grad_noise.txt) up to 1.4e-4 of the
-    tensor scale and 4e-2 relative on single ill-conditioned scale/rotation entries (cancellation in the conic ->
+    ITS gradients differ run to run: measured ref-vs-ref on B200 (profiles/r01_grad_noise*.txt) up to 7e-3 of the
+    tensor scale and 40 % relative on single ill-conditioned scale/rotation entries (cancellation in the conic ->
     cov3D chain), so an elementwise 1e-3 relative bar is not met by the reference against itself.  The bar here:
       (1) aggregate: ||a - b||_2 <= 1e-3 ||b||_2               (the stated 1e-3, order-independent; measured ~1e-6..2e-4)
-      (2) every entry: |a - b| <= 1e-3 |b| + 1e-3 * scale      (no outliers)
+      (2) every entry: |a - b| <= 1e-3 |b| + max(4 x the reference's own max deviation between two runs (b vs b2),
+          1e-5 * scale); without a second reference run the floor is 1e-3 * scale
       (3) 99.9 % of entries: |a - b| <= 1e-3 |b| + 1e-5 * scale (the elementwise 1e-3 bar up to reference noise)"""
     a, b = a.double(), b.double()
     scale = b.abs().max().item()
     err = (a - b).abs()
     l2 = (err.pow(2).sum().sqrt() / b.pow(2).sum().sqrt().clamp_min(1e-30)).item()
     assert l2 <= 1e-3, f"{name}: relative L2 error {l2:.3e}"
-    loose = err <= GRAD_RTOL * b.abs() + max(scale * 1e-3, 1e-12)
+    floor = scale * 1e-3 if b2 is None else max(4.0 * (b - b2.double()).abs().max().item(), scale * 1e-5)
+    loose = err <= GRAD_RTOL * b.abs() + max(floor, 1e-12)
     strict = err <= GRAD_RTOL * b.abs() + max(scale * 1e-5, 1e-12)
-    assert bool(loose.all()), f"{name}: max err {err.max().item():.3e} (scale {scale:.3e})"
+    assert bool(loose.all()), f"{name}: max err {err.max().item():.3e} (scale {scale:.3e}, floor {floor:.3e})"
     frac_bad = 1.0 - strict.double().mean().item()
     assert frac_bad <= 1e-3, f"{name}: {frac_bad:.3e} of entries outside rtol {GRAD_RTOL} with the strict floor"
 
@@ -113,12 +115,13 @@ def test_forward_backward_vs_reference(mods, name, kw, bgv):
 
     dgr.clear_geometry_cache()
     c_ref, r_ref, g_ref = run(ref)
+    _, _, g_ref2 = run(ref)          # second run of the reference: its own atomic-order noise calibrates the floor
     c_new, r_new, g_new = run(dgr)
     assert torch.equal(r_ref, r_new)
     assert (c_ref - c_new).abs().max().item() <= IMG_TOL
-    for nm, a, b in zip(("means3D", "means2D", "colors", "opacities", "scales", "rotations"), g_new, g_ref):
+    for nm, a, b, b2 in zip(("means3D", "means2D", "colors", "opacities", "scales", "rotations"), g_new, g_ref, g_ref2):
         assert a is not None, nm
-        _grad_close(a, b, nm)
+        _grad_close(a, b, nm, b2)
 
 
 def test_n_contrib_and_final_T(mods):
@@ -190,11 +193,12 @@ def test_six_call_render_pattern_gradient_sum(mods):
     dgr.clear_geometry_cache()
     launches0 = 0
     i_ref, g_ref = run(ref)
+    _, g_ref2 = run(ref)
     i_new, g_new = run(dgr)
     for a, b in zip(i_new, i_ref):
         assert (a - b).abs().max().item() <= IMG_TOL
-    for k, (a, b) in enumerate(zip(g_new, g_ref)):
-        _grad_close(a, b, f"grad[{k}]")
+    for k, (a, b, b2) in enumerate(zip(g_new, g_ref, g_ref2)):
+        _grad_close(a, b, f"grad[{k}]", b2)
 
 
 def test_mark_visible_and_empty(mods):
@@ -253,6 +257,7 @@ def test_render_mirror_dropin_vs_fused_vs_reference(mods):
         return {k: out[k].detach() for k in keys + ("alpha",)}, grads, out["radii"]
 
     o_ref, g_ref, r_ref = run("ref")
+    _, g_ref2, _ = run("ref")
     for kind in ("dropin", "fused"):
         o, g, r = run(kind)
         assert torch.equal(r, r_ref)
@@ -261,6 +266,6 @@ def test_render_mirror_dropin_vs_fused_vs_reference(mods):
             assert (o[k] - o_ref[k]).abs().max().item() <= 2e-5 * scale, f"{kind} {k}"
         names = ("means3D", "opacity", "scales", "rotations", "albedo", "roughness", "metalness", "env_sh", "sky_sh",
                  "viewspace_points")
-        for nm, a, b in zip(names, g, g_ref):
+        for nm, a, b, b2 in zip(names, g, g_ref, g_ref2):
             assert a is not None and b is not None, nm
-            _grad_close(a, b, f"{kind}:{nm}")
+            _grad_close(a, b, f"{kind}:{nm}", b2)
