@@ -186,6 +186,12 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
 // K5 backward
 // =================================================================================================
 constexpr int BWD_WARPS = TILE_PIX / 32;
+// true : the warp-reduced partials leave the warp as one RED per (warp, splat, component) straight to L2
+// false: they are parked in warp-private smem and flushed as one RED per (tile, splat, component)
+#ifndef R3DGW_BWD_DIRECT_RED
+#define R3DGW_BWD_DIRECT_RED 0
+#endif
+constexpr bool BWD_DIRECT = R3DGW_BWD_DIRECT_RED != 0;
 
 template <int C, int BATCH>
 struct BwdSmem {
@@ -193,7 +199,7 @@ struct BwdSmem {
     float4 A[2][BATCH];
     float4 B[2][BATCH];
     float feat[2][BATCH * C];
-    float acc[BWD_WARPS][BATCH * NV];
+    float acc[BWD_DIRECT ? 1 : BWD_WARPS][BWD_DIRECT ? 1 : BATCH * NV];
     uint32_t mask[BWD_WARPS][(BATCH + 31) / 32];
     uint32_t red[BWD_WARPS];
     uint64_t bar[2];
@@ -256,6 +262,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
         bg_dot_dpixel += bg_color[ch] * dL_dpixel[ch];
     }
     float last_alpha = 0;
+    bool bg_nonzero = false;   // kernel-uniform: the background term vanishes for the usual black background
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) bg_nonzero |= (bg_color[ch] != 0.f);
     const float ddelx_dx = 0.5 * W;
     const float ddely_dy = 0.5 * H;
 
@@ -271,9 +280,11 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 #pragma unroll
             for (int ch = 0; ch < C; ++ch) s.feat[buf][tid * C + ch] = f[ch];
         }
-        __syncthreads();   // features staged; previous round's flush finished -> acc / mask / other buffer free
-        if (lane < (BATCH + 31) / 32) s.mask[warp][lane] = 0;
-        __syncwarp();
+        __syncthreads();   // features staged; previous round (and its flush) finished -> other buffer / acc / mask free
+        if constexpr (!BWD_DIRECT) {
+            if (lane < (BATCH + 31) / 32) s.mask[warp][lane] = 0;
+            __syncwarp();
+        }
         if (tid == 0 && i + 1 < rounds) {
             const int nb = buf ^ 1;
             const int nhi = total - (i + 1) * BATCH;
@@ -314,7 +325,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 #pragma unroll
                         for (int q = 0; q < NV; ++q) g[q] = 0.f;
                         if (valid) {
-                            T = T / (1.f - alpha);   // same expression as the reference: per-pixel terms stay bit-identical
+                            // 1/(1-alpha) once (alpha <= 0.99): the reference divides twice; the 2-ulp reciprocal is far
+                            // inside the gradient tolerance and the reference's own atomic-order noise
+                            const float inv_1ma = __fdividef(1.f, 1.f - alpha);
+                            T = T * inv_1ma;
                             const float dchannel_dcolor = alpha * T;
                             float dL_dalpha = 0.0f;
 #pragma unroll
@@ -328,7 +342,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                             }
                             dL_dalpha *= T;
                             last_alpha = alpha;
-                            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                            if (bg_nonzero) dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
                             const float dL_dG = b.y * dL_dalpha;
                             const float gdx = G * d.x;
                             const float gdy = G * d.y;
@@ -336,19 +350,35 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                             const float dG_ddely = -gdy * b.x - gdx * a.w;
                             g[0] = dL_dG * dG_ddelx * ddelx_dx;
                             g[1] = dL_dG * dG_ddely * ddely_dy;
-                            g[2] = -0.5f * gdx * d.x * dL_dG;
-                            g[3] = -0.5f * gdx * d.y * dL_dG;
-                            g[4] = -0.5f * gdy * d.y * dL_dG;
+                            const float hG = -0.5f * dL_dG;
+                            g[2] = hG * gdx * d.x;
+                            g[3] = hG * gdx * d.y;
+                            g[4] = hG * gdy * d.y;
                             g[5] = G * dL_dalpha;
                         }
-                        float* slot = &s.acc[warp][jj * NV];
-                        warp_reduce_multi<NV>(g, lane, [&](int vi, float v) { slot[vi] = v; });
-                        my_mask |= 1u << bit;
+                        if constexpr (BWD_DIRECT) {
+                            const uint32_t id = __float_as_uint(b.w);
+                            warp_reduce_multi<NV>(g, lane, [&](int vi, float v) {
+                                float* dst;
+                                if (vi < 2) dst = dL_dmean2D + (size_t)id * 3 + vi;
+                                else if (vi < 5) dst = dL_dconic2D + (size_t)id * 4 + (vi == 4 ? 3 : vi - 2);
+                                else if (vi == 5) dst = dL_dopacity + id;
+                                else dst = dL_dfeatures + (size_t)id * C + (vi - 6);
+                                atomicAdd(dst, v);
+                            });
+                        } else {
+                            float* slot = &s.acc[warp][jj * NV];
+                            warp_reduce_multi<NV>(g, lane, [&](int vi, float v) { slot[vi] = v; });
+                            my_mask |= 1u << bit;
+                        }
                     }
                 }
-                if (lane == 0) s.mask[warp][c0 >> 5] = my_mask;
+                if constexpr (!BWD_DIRECT) {
+                    if (lane == 0) s.mask[warp][c0 >> 5] = my_mask;
+                }
             }
         }
+        if constexpr (BWD_DIRECT) continue;
         __syncthreads();   // all warps' partial sums parked
 
         // flush: one atomic per (splat, component) that received anything in this tile
@@ -429,10 +459,13 @@ int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4*
                             float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream) {
     switch (C) {
 #define R3DGW_BWD_CASE(N, BT) case N: return launch_backward<N, BT>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures, stream);
-        R3DGW_BWD_CASE(1, 128) R3DGW_BWD_CASE(2, 128) R3DGW_BWD_CASE(3, 128) R3DGW_BWD_CASE(4, 128)
-        R3DGW_BWD_CASE(6, 128) R3DGW_BWD_CASE(8, 64) R3DGW_BWD_CASE(9, 64) R3DGW_BWD_CASE(12, 64)
-        R3DGW_BWD_CASE(15, 64) R3DGW_BWD_CASE(16, 64) R3DGW_BWD_CASE(18, 32) R3DGW_BWD_CASE(24, 32)
-        R3DGW_BWD_CASE(27, 32) R3DGW_BWD_CASE(32, 32)
+#define BT_(direct, parked) (BWD_DIRECT ? direct : parked)
+        R3DGW_BWD_CASE(1, BT_(256, 128)) R3DGW_BWD_CASE(2, BT_(256, 128)) R3DGW_BWD_CASE(3, BT_(256, 128))
+        R3DGW_BWD_CASE(4, BT_(256, 128)) R3DGW_BWD_CASE(6, BT_(256, 128)) R3DGW_BWD_CASE(8, BT_(128, 64))
+        R3DGW_BWD_CASE(9, BT_(128, 64)) R3DGW_BWD_CASE(12, BT_(128, 64)) R3DGW_BWD_CASE(15, BT_(128, 64))
+        R3DGW_BWD_CASE(16, BT_(128, 64)) R3DGW_BWD_CASE(18, BT_(64, 32)) R3DGW_BWD_CASE(24, BT_(64, 32))
+        R3DGW_BWD_CASE(27, BT_(64, 32)) R3DGW_BWD_CASE(32, BT_(64, 32))
+#undef BT_
 #undef R3DGW_BWD_CASE
         default: return R3DGW_ERR_UNSUPPORTED;
     }

@@ -74,11 +74,17 @@ class _Holder:
         self.t = None
 
         def _cb(_ctx, nbytes):
-            try:
-                self.t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
-                return self.t.data_ptr()
-            except Exception:   # noqa: BLE001 - surfaces as R3DGW_ERR_ALLOC
-                return 0
+            for attempt in (0, 1):
+                try:
+                    self.t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
+                    return self.t.data_ptr()
+                except torch.OutOfMemoryError:
+                    if attempt == 0:        # multi-GB state buffers: give cached-but-fragmented blocks back and retry once
+                        clear_geometry_cache()
+                        torch.cuda.empty_cache()
+                except Exception:   # noqa: BLE001 - surfaces as R3DGW_ERR_ALLOC
+                    break
+            return 0
 
         self.cb = _nat.ALLOC_FN(_cb)
 

@@ -20,7 +20,7 @@ BASE_SEED = 20261104
 CONFIGS = {
     "A": dict(cfg_id=0, P=200_000, W=800, H=600, sigma_px=2.0),
     "B": dict(cfg_id=1, P=1_000_000, W=1920, H=1080, sigma_px=2.0),
-    "E": dict(cfg_id=4, P=6_000_000, W=3840, H=2160, sigma_px=10.0),
+    "E": dict(cfg_id=4, P=6_000_000, W=3840, H=2160, sigma_px=6.0),
     "tiny": dict(cfg_id=10, P=2_000, W=160, H=96, sigma_px=2.0),
     "small": dict(cfg_id=11, P=20_000, W=320, H=240, sigma_px=2.0),
 }
