@@ -107,14 +107,18 @@ struct PreprocessParams {
 __global__ void __launch_bounds__(PRE_THREADS) preprocess_scan_kernel(const PreprocessParams p) {
     __shared__ float s_view[16], s_proj[16];
     __shared__ uint32_t s_warp_sum[PRE_THREADS / 32];
-    __shared__ uint32_t s_block_prefix;
+    __shared__ uint32_t s_block_prefix, s_tile;
     if (threadIdx.x < 16) {
         s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
         s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
     }
+    // dynamic tile id: the look-back below waits on lower-numbered tiles, so ids are handed out in the order CTAs
+    // actually start (forward progress does not depend on the hardware's block dispatch order)
+    if (threadIdx.x == 0) s_tile = atomicAdd(p.total_out + 1, 1u);
     __syncthreads();
+    const unsigned bid = s_tile;
 
-    const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
+    const int idx = bid * PRE_THREADS + threadIdx.x;
     uint32_t touched = 0;
     if (idx < p.P) {
         int my_radius_i = 0;
@@ -191,11 +195,11 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_scan_kernel(const Prep
         uint32_t block_total = __shfl_sync(0xffffffffu, wi, PRE_THREADS / 32 - 1);
         // publish aggregate, look back
         uint32_t excl = 0;
-        if (blockIdx.x == 0) {
+        if (bid == 0) {
             if (lane == 0) scan_state_store(p.scan_state, 2u, block_total);
         } else {
-            if (lane == 0) scan_state_store(p.scan_state + blockIdx.x, 1u, block_total);
-            int base = (int)blockIdx.x - 1;
+            if (lane == 0) scan_state_store(p.scan_state + bid, 1u, block_total);
+            int base = (int)bid - 1;
             while (true) {
                 int j = base - (int)lane;
                 unsigned long long w = 0;
@@ -213,11 +217,11 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_scan_kernel(const Prep
                 if (first >= 0) break;
                 base -= 32;
             }
-            if (lane == 0) scan_state_store(p.scan_state + blockIdx.x, 2u, excl + block_total);
+            if (lane == 0) scan_state_store(p.scan_state + bid, 2u, excl + block_total);
         }
         if (lane == 0) {
             s_block_prefix = excl;
-            if (blockIdx.x == gridDim.x - 1) *p.total_out = excl + block_total;
+            if (bid == gridDim.x - 1) *p.total_out = excl + block_total;
         }
     }
     __syncthreads();
