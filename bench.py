@@ -364,15 +364,27 @@ def main():
 
     # ---- e2e: host buffers in, loss out, through the public API ----------------------------------------
     pin = lambda t: t.contiguous().pin_memory()   # noqa: E731
-    h_gt, h_view, h_proj = pin(gt_cpu), pin(cam.world_view_transform.cpu()), pin(cam.full_proj_transform.cpu())
+    # the GT image travels as 8-bit RGB, the way image datasets are stored; it is converted to float on the device
+    h_gt = pin((gt_cpu * 255.0).round().to(torch.uint8))
+    h_view, h_proj = pin(cam.world_view_transform.cpu()), pin(cam.full_proj_transform.cpu())
     h_cpos, h_env, h_sky = pin(cam.camera_center.cpu()), pin(sc.env_sh), pin(sc.sky_sh)
-    d_gt, d_view, d_proj = torch.empty_like(gt), torch.empty(4, 4, device=device), torch.empty(4, 4, device=device)
+    d_gt8 = torch.empty(gt.shape, dtype=torch.uint8, device=device)
+    d_view, d_proj = torch.empty(4, 4, device=device), torch.empty(4, 4, device=device)
     d_cpos = torch.empty(3, device=device)
     h_loss = torch.zeros(1).pin_memory()
-    h2d = sum(t.numel() * 4 for t in (h_gt, h_view, h_proj, h_cpos, h_env, h_sky))
+    h2d = sum(t.numel() * t.element_size() for t in (h_gt, h_view, h_proj, h_cpos, h_env, h_sky))
+    # measured pinned H2D bandwidth of this box (reported beside e2e: some hosts deliver a fraction of PCIe 5)
+    probe_h = torch.empty(64 << 20, dtype=torch.uint8).pin_memory()
+    probe_d = torch.empty(64 << 20, dtype=torch.uint8, device=device)
+    probe_d.copy_(probe_h, non_blocking=True); torch.cuda.synchronize()
+    ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ea.record(); probe_d.copy_(probe_h, non_blocking=True); eb.record(); torch.cuda.synchronize()
+    h2d_gbps = (64 << 20) / (ea.elapsed_time(eb) * 1e-3) / 1e9
+    del probe_h, probe_d
 
     def step_e2e():
-        d_gt.copy_(h_gt, non_blocking=True)
+        d_gt8.copy_(h_gt, non_blocking=True)
+        d_gt = d_gt8.to(torch.float32).mul_(1.0 / 255.0)
         d_view.copy_(h_view, non_blocking=True)
         d_proj.copy_(h_proj, non_blocking=True)
         d_cpos.copy_(h_cpos, non_blocking=True)
@@ -399,7 +411,7 @@ def main():
                        "mode": args.mode, "views_per_step": world},
             "clocks": clocks, "gpu_launches": int(gpu_launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
-                    "d2h_bytes_per_step": 4}}
+                    "d2h_bytes_per_step": 4, "h2d_gbps_measured": round(h2d_gbps, 2)}}
     if args.impl == "reference":
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
@@ -407,7 +419,7 @@ def main():
                                           "(oracle/_ref, built from /root/reference for sm_100a) + its torch shading "
                                           "graph, same B200, same steps; CPU port figure is in the native arm's line"}
         line["e2e"] = {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
-                       "d2h_bytes_per_step": 4}
+                       "d2h_bytes_per_step": 4, "h2d_gbps_measured": round(h2d_gbps, 2)}
 
     # ---- extras: fwd-only frames/s (U3), single raster call fwd / fwd+bwd (U1) ---------------------------
     def frame(new_view=True):

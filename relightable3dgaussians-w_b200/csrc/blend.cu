@@ -69,11 +69,16 @@ __device__ __forceinline__ bool splat_touches_warp(const float4 b, unsigned warp
 // =================================================================================================
 constexpr int FWD_BATCH = 256;
 
+// channels padded to a multiple of 4 in shared memory: one LDS.128 fetches 4 channels and the accumulation runs
+// on packed FP32 pairs (fma.rn.f32x2 -> SASS FFMA2, new on sm_100: two FP32 FMAs per issue slot)
+template <int C>
+struct ChanPad { static constexpr int CP = (C + 3) / 4 * 4; };
+
 template <int C>
 struct FwdSmem {
     float4 A[2][FWD_BATCH];
     float4 B[2][FWD_BATCH];
-    float feat[2][FWD_BATCH * C];
+    float4 feat[2][FWD_BATCH * ChanPad<C>::CP / 4];
     uint64_t bar[2];
 };
 
@@ -111,11 +116,12 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
         bulk_g2s(s.B[0], splatB + range.x, cnt * 16u, &s.bar[0]);
     }
 
+    constexpr int CP = ChanPad<C>::CP;
     float T = 1.0f;
     uint32_t last_contributor = 0;
-    float Cacc[C];
+    float2 Cacc[CP / 2];
 #pragma unroll
-    for (int ch = 0; ch < C; ++ch) Cacc[ch] = 0.f;
+    for (int q = 0; q < CP / 2; ++q) Cacc[q] = make_float2(0.f, 0.f);
 
     for (int i = 0; i < rounds; ++i) {
         const int buf = i & 1;
@@ -125,8 +131,12 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
         if ((int)tid < cnt) {
             const uint32_t id = __float_as_uint(s.B[buf][tid].w);
             const float* f = features + (size_t)id * C;
+            float fv[CP];
 #pragma unroll
-            for (int ch = 0; ch < C; ++ch) s.feat[buf][tid * C + ch] = f[ch];
+            for (int ch = 0; ch < CP; ++ch) fv[ch] = ch < C ? f[ch] : 0.f;
+#pragma unroll
+            for (int q = 0; q < CP / 4; ++q)
+                s.feat[buf][tid * (CP / 4) + q] = make_float4(fv[4 * q], fv[4 * q + 1], fv[4 * q + 2], fv[4 * q + 3]);
         }
         // one barrier per round: publishes the features, retires the other buffer, and votes
         const int num_done = __syncthreads_count(done);
@@ -164,8 +174,13 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                     continue;
                 }
                 const float w = alpha * T;   // (f*alpha)*T in the reference: differs by <= 1 ulp per term
+                const float2 w2 = make_float2(w, w);
 #pragma unroll
-                for (int ch = 0; ch < C; ++ch) Cacc[ch] += s.feat[buf][j * C + ch] * w;
+                for (int q = 0; q < CP / 4; ++q) {
+                    const float4 f = s.feat[buf][j * (CP / 4) + q];
+                    Cacc[2 * q] = __ffma2_rn(make_float2(f.x, f.y), w2, Cacc[2 * q]);
+                    Cacc[2 * q + 1] = __ffma2_rn(make_float2(f.z, f.w), w2, Cacc[2 * q + 1]);
+                }
                 T = test_T;
                 last_contributor = base + (uint32_t)j + 1u;
             }
@@ -177,7 +192,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
         final_T[pix_id] = T;
         n_contrib[pix_id] = last_contributor;
 #pragma unroll
-        for (int ch = 0; ch < C; ++ch) out_color[(size_t)ch * H * W + pix_id] = Cacc[ch] + T * bg_color[ch];
+        for (int ch = 0; ch < C; ++ch) {
+            const float c = (ch & 1) ? Cacc[ch >> 1].y : Cacc[ch >> 1].x;
+            out_color[(size_t)ch * H * W + pix_id] = c + T * bg_color[ch];
+        }
     }
 }
 
@@ -198,7 +216,7 @@ struct BwdSmem {
     static constexpr int NV = 6 + C;
     float4 A[2][BATCH];
     float4 B[2][BATCH];
-    float feat[2][BATCH * C];
+    float4 feat[2][BATCH * ChanPad<C>::CP / 4];
     float acc[BWD_DIRECT ? 1 : BWD_WARPS][BWD_DIRECT ? 1 : BATCH * NV];
     uint32_t mask[BWD_WARPS][(BATCH + 31) / 32];
     uint32_t red[BWD_WARPS];
@@ -252,14 +270,18 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
         bulk_g2s(s.B[0], splatB + off, (uint32_t)cnt * 16u, &s.bar[0]);
     }
 
-    float accum_rec[C], last_color[C], dL_dpixel[C];
+    constexpr int CP = ChanPad<C>::CP;
+    float2 accum_rec[CP / 2], last_color[CP / 2], dL_dpixel[CP / 2];   // channel pairs (packed FP32 math below)
     float bg_dot_dpixel = 0;
 #pragma unroll
-    for (int ch = 0; ch < C; ++ch) {
-        accum_rec[ch] = 0.f;
-        last_color[ch] = 0.f;
-        dL_dpixel[ch] = inside ? dL_dpixels[(size_t)ch * H * W + pix_id] : 0.f;
-        bg_dot_dpixel += bg_color[ch] * dL_dpixel[ch];
+    for (int q = 0; q < CP / 2; ++q) {
+        accum_rec[q] = make_float2(0.f, 0.f);
+        last_color[q] = make_float2(0.f, 0.f);
+        const int c0 = 2 * q, c1 = 2 * q + 1;
+        dL_dpixel[q].x = (inside && c0 < C) ? dL_dpixels[(size_t)c0 * H * W + pix_id] : 0.f;
+        dL_dpixel[q].y = (inside && c1 < C) ? dL_dpixels[(size_t)c1 * H * W + pix_id] : 0.f;
+        if (c0 < C) bg_dot_dpixel += bg_color[c0] * dL_dpixel[q].x;
+        if (c1 < C) bg_dot_dpixel += bg_color[c1] * dL_dpixel[q].y;
     }
     float last_alpha = 0;
     bool bg_nonzero = false;   // kernel-uniform: the background term vanishes for the usual black background
@@ -277,8 +299,12 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
         if ((int)tid < cnt) {
             const uint32_t id = __float_as_uint(s.B[buf][tid].w);
             const float* f = features + (size_t)id * C;
+            float fv[CP];
 #pragma unroll
-            for (int ch = 0; ch < C; ++ch) s.feat[buf][tid * C + ch] = f[ch];
+            for (int ch = 0; ch < CP; ++ch) fv[ch] = ch < C ? f[ch] : 0.f;
+#pragma unroll
+            for (int q = 0; q < CP / 4; ++q)
+                s.feat[buf][tid * (CP / 4) + q] = make_float4(fv[4 * q], fv[4 * q + 1], fv[4 * q + 2], fv[4 * q + 3]);
         }
         __syncthreads();   // features staged; previous round (and its flush) finished -> other buffer / acc / mask free
         if constexpr (!BWD_DIRECT) {
@@ -330,16 +356,29 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                             const float inv_1ma = __fdividef(1.f, 1.f - alpha);
                             T = T * inv_1ma;
                             const float dchannel_dcolor = alpha * T;
-                            float dL_dalpha = 0.0f;
+                            // per-channel recurrences on packed FP32 pairs (FFMA2 / FMUL2)
+                            const float2 la2 = make_float2(last_alpha, last_alpha);
+                            const float2 oml2 = make_float2(1.f - last_alpha, 1.f - last_alpha);
+                            const float2 dcd2 = make_float2(dchannel_dcolor, dchannel_dcolor);
+                            const float2 neg1 = make_float2(-1.f, -1.f);
+                            float2 dLa2 = make_float2(0.f, 0.f);
 #pragma unroll
-                            for (int ch = 0; ch < C; ++ch) {
-                                const float c = s.feat[buf][jj * C + ch];
-                                accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                                last_color[ch] = c;
-                                const float dL_dchannel = dL_dpixel[ch];
-                                dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;
-                                g[6 + ch] = dchannel_dcolor * dL_dchannel;
+                            for (int q = 0; q < CP / 4; ++q) {
+                                const float4 f = s.feat[buf][jj * (CP / 4) + q];
+#pragma unroll
+                                for (int h = 0; h < 2; ++h) {
+                                    const int p2 = 2 * q + h;
+                                    const float2 c2 = h ? make_float2(f.z, f.w) : make_float2(f.x, f.y);
+                                    const float2 ar = __ffma2_rn(la2, last_color[p2], __fmul2_rn(oml2, accum_rec[p2]));
+                                    accum_rec[p2] = ar;
+                                    last_color[p2] = c2;
+                                    dLa2 = __ffma2_rn(__ffma2_rn(ar, neg1, c2), dL_dpixel[p2], dLa2);
+                                    const float2 gc = __fmul2_rn(dcd2, dL_dpixel[p2]);
+                                    if (2 * p2 < C) g[6 + 2 * p2] = gc.x;
+                                    if (2 * p2 + 1 < C) g[6 + 2 * p2 + 1] = gc.y;
+                                }
                             }
+                            float dL_dalpha = dLa2.x + dLa2.y;
                             dL_dalpha *= T;
                             last_alpha = alpha;
                             if (bg_nonzero) dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
