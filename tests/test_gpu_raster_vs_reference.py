@@ -348,3 +348,100 @@ def test_stress_full_size_properties(native_lib):
     assert abs(lhs - rhs) <= 1e-4 * max(abs(lhs), abs(rhs), 1e-12), (lhs, rhs)
     assert torch.isfinite(op.grad).all() and torch.isfinite(m2.grad).all()
     assert bool((m2.grad[radii == 0] == 0).all())                                    # culled Gaussians get no gradient
+
+
+@pytest.mark.parametrize("deg", [0, 1, 2, 3])
+def test_sh_colours_path_vs_reference(mods, deg):
+    """In-rasterizer SH -> RGB (forward.cu:20-71, backward.cu:20-139): unused by the relighting repo (it always passes
+    colors_precomp) but part of the API; fwd bit-compatible decisions, grads w.r.t. SHs and means3D."""
+    dgr, ref, rl = mods
+    from r3dgw_b200.synthetic import make_scene
+    sc = make_scene("small", seed_offset=40 + deg).to("cuda")
+    H, W = sc.camera.image_height, sc.camera.image_width
+    gen = torch.Generator(device="cpu").manual_seed(8)
+    M = 16
+    shs0 = (torch.randn(sc.P, M, 3, generator=gen) * 0.3).cuda()
+    dL = (torch.randn(3, H, W, generator=gen) * 1e-3).cuda()
+
+    def run(mod):
+        cam = sc.camera
+        s = mod.GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, sc.bg, 1.3, cam.world_view_transform,
+                                              cam.full_proj_transform, deg, cam.camera_center, False)
+        m3, sh, op, scl, rot = [t.clone().requires_grad_(True) for t in (sc.means3D, shs0, sc.opacities, sc.scales, sc.rotations)]
+        m2 = torch.zeros_like(m3, requires_grad=True)
+        img, radii = mod.GaussianRasterizer(s)(means3D=m3, means2D=m2, opacities=op, shs=sh, scales=scl, rotations=rot)
+        img.backward(dL)
+        return img.detach(), radii, [m3.grad, sh.grad, op.grad, scl.grad, rot.grad]
+
+    dgr.clear_geometry_cache()
+    i_r, r_r, g_r = run(ref)
+    _, _, g_r2 = run(ref)
+    i_n, r_n, g_n = run(dgr)
+    assert torch.equal(r_r, r_n)
+    assert (i_r - i_n).abs().max().item() <= IMG_TOL
+    for nm, a, b, b2 in zip(("means3D", "shs", "opacities", "scales", "rotations"), g_n, g_r, g_r2):
+        _grad_close(a, b, f"deg{deg}:{nm}", b2)
+
+
+def test_cov3d_precomp_path_vs_reference(mods):
+    """pipe.compute_cov3D_python = True (gaussian_renderer/__init__.py:113-115): cov3D_precomp instead of scale/rot."""
+    dgr, ref, rl = mods
+    from r3dgw_b200.synthetic import make_scene
+    sc = make_scene("small", seed_offset=55).to("cuda")
+    H, W = sc.camera.image_height, sc.camera.image_width
+    # Sigma = R S S^T R^T, upper triangle (utils/general_utils.py build_scaling_rotation / strip_symmetric)
+    q = sc.rotations
+    r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    Rm = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y), 2 * (x * y + r * z),
+                      1 - 2 * (x * x + z * z), 2 * (y * z - r * x), 2 * (x * z - r * y), 2 * (y * z + r * x),
+                      1 - 2 * (x * x + y * y)], dim=1).view(-1, 3, 3)
+    L = Rm * sc.scales.unsqueeze(1)
+    Sig = L @ L.transpose(1, 2)
+    cov0 = torch.stack([Sig[:, 0, 0], Sig[:, 0, 1], Sig[:, 0, 2], Sig[:, 1, 1], Sig[:, 1, 2], Sig[:, 2, 2]], dim=1).contiguous()
+    gen = torch.Generator(device="cpu").manual_seed(9)
+    dL = (torch.randn(3, H, W, generator=gen) * 1e-3).cuda()
+
+    def run(mod):
+        m3, col, op, cov = [t.clone().requires_grad_(True) for t in (sc.means3D, sc.colors, sc.opacities, cov0)]
+        m2 = torch.zeros_like(m3, requires_grad=True)
+        img, radii = mod.GaussianRasterizer(_settings(mod, sc))(means3D=m3, means2D=m2, opacities=op, colors_precomp=col,
+                                                               cov3D_precomp=cov)
+        img.backward(dL)
+        return img.detach(), radii, [m3.grad, col.grad, op.grad, cov.grad, m2.grad]
+
+    dgr.clear_geometry_cache()
+    i_r, r_r, g_r = run(ref)
+    _, _, g_r2 = run(ref)
+    i_n, r_n, g_n = run(dgr)
+    assert torch.equal(r_r, r_n)
+    assert (i_r - i_n).abs().max().item() <= IMG_TOL
+    for nm, a, b, b2 in zip(("means3D", "colors", "opacities", "cov3D", "means2D"), g_n, g_r, g_r2):
+        _grad_close(a, b, f"cov3D_precomp:{nm}", b2)
+
+
+def test_all_culled_and_tiny_images(mods):
+    """Edge cases: every Gaussian behind the camera (R = 0), a 1x1 and a 17x5 image, P not a multiple of 256."""
+    dgr, ref, rl = mods
+    from r3dgw_b200.synthetic import make_scene
+    sc = make_scene("tiny", P=777).to("cuda")
+    behind = sc.means3D.clone()
+    behind[:, 2] = -behind[:, 2].abs() - 1.0
+    rast = dgr.GaussianRasterizer(_settings(dgr, sc, bg=torch.tensor([0.2, 0.4, 0.6], device="cuda")))
+    dgr.clear_geometry_cache()
+    m3 = behind.requires_grad_(True)
+    img, radii = rast(means3D=m3, means2D=torch.zeros_like(m3), opacities=sc.opacities, colors_precomp=sc.colors,
+                      scales=sc.scales, rotations=sc.rotations)
+    assert int(radii.abs().sum()) == 0 and dgr.last_geometry_state().R == 0
+    assert torch.allclose(img[:, 0, 0], torch.tensor([0.2, 0.4, 0.6], device="cuda"))
+    img.sum().backward()
+    assert float(m3.grad.abs().sum()) == 0.0
+    for (W, H) in ((1, 1), (17, 5)):
+        sc2 = make_scene("tiny", P=777, W=W, H=H, seed_offset=60 + W).to("cuda")
+        dgr.clear_geometry_cache()
+        R_ref, c_ref, r_ref, *_ = _run_ref(ref, sc2, sc2.colors)
+        with torch.no_grad():
+            c, r = dgr.GaussianRasterizer(_settings(dgr, sc2))(means3D=sc2.means3D, means2D=torch.zeros_like(sc2.means3D),
+                                                                 opacities=sc2.opacities, colors_precomp=sc2.colors,
+                                                                 scales=sc2.scales, rotations=sc2.rotations)
+        assert torch.equal(r, r_ref) and dgr.last_geometry_state().R == R_ref
+        assert (c - c_ref).abs().max().item() <= IMG_TOL
