@@ -496,8 +496,14 @@ def main():
         peak = float(peaks.get("hbm_gbs", 6650.0))
         ab = algorithmic_bytes(top, P, Pv, Rn, N, tiles, C, n_pass)
         ach = ab / (kern[top]["avg_launch_ms"] * 1e-3) / 1e9
+        traffic = None       # dram__bytes_read+write per launch from the committed `ncu --set full` capture (C = 3, config B)
+        try:
+            if args.workload == "B" and C == 3:
+                traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))[top]["dram_traffic_bytes_per_launch"]
+        except Exception:   # noqa: BLE001
+            pass
         line["roofline"] = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s",
-                            "frac": ach / peak, "traffic": None,
+                            "frac": ach / peak, "traffic": traffic,
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650",
                             "algorithmic_bytes_per_launch": ab, "avg_launch_ms": kern[top]["avg_launch_ms"],
                             "share_of_step_kernel_time": kern[top]["ms_per_step"] / step_kernel_ms}
