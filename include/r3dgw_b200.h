@@ -224,6 +224,39 @@ int r3dgw_shade_backward(const r3dgw_shade_args* a,
                          float* dL_droughness, float* dL_dmetalness,
                          float* dL_denv_sh, float* dL_dsky_sh, void* stream);
 
+/* ---- image-space post-ops of the training step ---------------------------------
+ * Replace torch graphs in the reference (paths relative to /root/reference):
+ *   r3dgw_ssim_l1_forward/backward   <- utils/loss_utils.py:27-36 (l1_loss) + :41-99 (ssim / _ssim, 11x11 Gaussian
+ *                                       window, sigma 1.5, zero padding, mask-weighted mean over mask == 1)
+ *   r3dgw_masked_l1_forward/backward <- utils/loss_utils.py:27-36 with mask or (1 - mask) (train.py:86-87)
+ *   r3dgw_depth_to_normal_forward/backward <- utils/graphics_utils.py:141-169 (depths_to_points + depth_to_normal)
+ * Images are f32[C,H,W], contiguous.  mask is f32 with channel stride mask_channel_stride elements (0 for a
+ * [1,H,W] mask broadcast over channels, H*W for a full [C,H,W] mask) or NULL (all ones).
+ * out / sums: device f32[4] = { mean of ssim_map over mask==1 (1 if none), masked L1 mean (0 if none),
+ * count(mask == 1), 1/count (0 if none) }.  workspace: r3dgw_image_loss_workspace_bytes(C,H,W) bytes.
+ * The per-block partial sums are reduced in a fixed order: results are bit-reproducible. */
+size_t r3dgw_image_loss_workspace_bytes(int C, int H, int W);
+int r3dgw_ssim_l1_forward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                          size_t mask_channel_stride,
+                          float* dmap,      /* f32[3,C,H,W] saved for backward, or NULL when no gradient is needed */
+                          char* workspace, float* out, void* stream);
+/* dL/dimg1 = coef[0] * d(ssim mean)/dimg1 + coef[1] * d(l1 mean)/dimg1; coef: device f32[2] (upstream grads). */
+int r3dgw_ssim_l1_backward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                           size_t mask_channel_stride, const float* dmap, const float* sums, const float* coef,
+                           float* dL_dimg1, void* stream);
+/* target may be NULL (zeros); complement != 0 uses (1 - mask).  out[0] is unused (0). */
+int r3dgw_masked_l1_forward(int C, int H, int W, const float* x, const float* target, const float* mask,
+                            size_t mask_channel_stride, int complement, char* workspace, float* out, void* stream);
+/* dL/dx = coef[0] * sign(x*m - t*m) * m / count; coef: device f32[1]. */
+int r3dgw_masked_l1_backward(int C, int H, int W, const float* x, const float* target, const float* mask,
+                             size_t mask_channel_stride, int complement, const float* sums, const float* coef,
+                             float* dL_dx, void* stream);
+/* depth f32[H,W]; rays: device f32[21] = intrins.inverse().T (3x3 row-major), c2w[:3,:3].T (3x3 row-major),
+ * rays_o[3] (graphics_utils.py:142-155); normal f32[H,W,3] (zero on the 1-pixel border). */
+int r3dgw_depth_to_normal_forward(int H, int W, const float* depth, const float* rays, float* normal, void* stream);
+int r3dgw_depth_to_normal_backward(int H, int W, const float* depth, const float* rays, const float* dL_dnormal,
+                                   float* dL_ddepth, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

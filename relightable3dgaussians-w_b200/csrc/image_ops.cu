@@ -1,0 +1,478 @@
+// image_ops.cu - image-space post-ops of the training step for sm_100a:
+//   * fused masked-L1 + 11x11 Gaussian SSIM, forward and backward
+//       reference: utils/loss_utils.py:27-36 (l1_loss), :41-99 (gaussian / create_window / ssim / _ssim) - a torch
+//       graph of five grouped 11x11 conv2d + ~25 elementwise kernels forward and as many backward;
+//   * depth_to_normal forward and backward
+//       reference: utils/graphics_utils.py:141-169 (depths_to_points, depth_to_normal) - meshgrid / matmul / cat /
+//       cross / normalize torch graph;
+//   * masked L1 against zero or a target (sky-BRDF regulariser, train.py:86-87).
+// All three are HBM-bound stencils on [C,H,W] images: every input is read once from HBM (halo re-reads hit L2),
+// the separable window runs out of shared memory, per-block partial sums are reduced in a FIXED order by a
+// one-block finalize kernel (no float atomics: the loss is bit-reproducible run to run).
+#include "common.cuh"
+
+namespace r3dgw {
+
+constexpr int IMG_T = 32;                  // output tile edge
+constexpr int WIN = 11, HALO = 5;          // window_size = 11, padding = 5 (loss_utils.py:53, 70)
+constexpr int IMG_IN = IMG_T + 2 * HALO;   // 42
+constexpr int IMG_THREADS = 256;
+constexpr int IMG_WARPS = IMG_THREADS / 32;
+
+// gaussian(11, 1.5) / sum, exactly the float32 values torch produces for loss_utils.py:41-44
+// (exp evaluated in double by Python, rounded to f32 by torch.Tensor, divided by the f32 sum)
+struct Window { float w[WIN]; };
+static Window make_window() {
+    Window g = {{0x1.0d956cp-10f, 0x1.f1fe02p-8f, 0x1.26eb18p-5f, 0x1.bff0fep-4f, 0x1.b43c3ep-3f, 0x1.10656p-2f,
+                 0x1.b43c3ep-3f, 0x1.bff0fep-4f, 0x1.26eb18p-5f, 0x1.f1fe02p-8f, 0x1.0d956cp-10f}};
+    return g;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// per-block partial sums -> partials[block*3 + {0,1,2}] (fixed order inside the block)
+__device__ __forceinline__ void block_partials3(float a, float b, float c, float (*red)[IMG_WARPS], float* dst) {
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+    if (lane == 0) { red[0][warp] = a; red[1][warp] = b; red[2][warp] = c; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < IMG_WARPS; ++w) s += red[threadIdx.x][w];
+        dst[threadIdx.x] = s;
+    }
+}
+
+// ---- SSIM + masked L1 forward ------------------------------------------------------------------------
+// out per pixel (only when dmap != NULL): mask * dS/dmu1, mask * dS/dE[x^2], mask * dS/dE[xy]  (S = ssim_map)
+__global__ void __launch_bounds__(IMG_THREADS) ssim_l1_forward_kernel(
+    int C, int H, int W, const float* __restrict__ img1, const float* __restrict__ img2,
+    const float* __restrict__ mask, size_t mask_cstride, Window win, float* __restrict__ dmap,
+    float* __restrict__ partials) {
+    __shared__ float s1[IMG_IN][IMG_IN + 1];
+    __shared__ float s2[IMG_IN][IMG_IN + 1];
+    __shared__ float hs[5][IMG_IN][IMG_T];
+    __shared__ float red[3][IMG_WARPS];
+    const int tid = threadIdx.x, c = blockIdx.z;
+    const int x0 = blockIdx.x * IMG_T, y0 = blockIdx.y * IMG_T;
+    const size_t plane = (size_t)H * W;
+    const float* p1 = img1 + (size_t)c * plane;
+    const float* p2 = img2 + (size_t)c * plane;
+    for (int i = tid; i < IMG_IN * IMG_IN; i += IMG_THREADS) {
+        const int r = i / IMG_IN, q = i - r * IMG_IN;
+        const int y = y0 + r - HALO, x = x0 + q - HALO;
+        const bool in = (x >= 0) && (x < W) && (y >= 0) && (y < H);   // zero padding (conv2d padding=5)
+        s1[r][q] = in ? p1[(size_t)y * W + x] : 0.f;
+        s2[r][q] = in ? p2[(size_t)y * W + x] : 0.f;
+    }
+    __syncthreads();
+    // horizontal pass: 42 rows x 32 columns, 5 moments
+    for (int i = tid; i < IMG_IN * IMG_T; i += IMG_THREADS) {
+        const int r = i >> 5, q = i & 31;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll
+        for (int k = 0; k < WIN; ++k) {
+            const float x = s1[r][q + k], y = s2[r][q + k];
+            const float wx = win.w[k] * x, wy = win.w[k] * y;
+            a0 += wx;
+            a1 += wy;
+            a2 = fmaf(wx, x, a2);
+            a3 = fmaf(wy, y, a3);
+            a4 = fmaf(wx, y, a4);
+        }
+        hs[0][r][q] = a0; hs[1][r][q] = a1; hs[2][r][q] = a2; hs[3][r][q] = a3; hs[4][r][q] = a4;
+    }
+    __syncthreads();
+    const int tx = tid & 31, ty = tid >> 5;
+    const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+    float accS = 0.f, accL = 0.f, accN = 0.f;
+#pragma unroll
+    for (int j = 0; j < IMG_T / IMG_WARPS; ++j) {
+        const int r = ty + IMG_WARPS * j;
+        const int y = y0 + r, x = x0 + tx;
+        float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+        for (int k = 0; k < WIN; ++k) {
+            const float w = win.w[k];
+            mu1 = fmaf(w, hs[0][r + k][tx], mu1);
+            mu2 = fmaf(w, hs[1][r + k][tx], mu2);
+            e11 = fmaf(w, hs[2][r + k][tx], e11);
+            e22 = fmaf(w, hs[3][r + k][tx], e22);
+            e12 = fmaf(w, hs[4][r + k][tx], e12);
+        }
+        if (x < W && y < H) {
+            const size_t idx = (size_t)y * W + x;
+            const float m = mask ? mask[(size_t)c * mask_cstride + idx] : 1.f;
+            // loss_utils.py:73-87
+            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu1_mu2 = mu1 * mu2;
+            const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1_mu2;
+            const float A1 = 2.f * mu1_mu2 + C1, A2 = 2.f * sigma12 + C2;
+            const float B1 = mu1_sq + mu2_sq + C1, B2 = sigma1_sq + sigma2_sq + C2;
+            const float S = (A1 * A2) / (B1 * B2);
+            accS += S * m;
+            const float a = s1[r + HALO][tx + HALO], b = s2[r + HALO][tx + HALO];
+            accL += fabsf(a * m - b * m);                      // loss_utils.py:34
+            accN += (m == 1.f) ? 1.f : 0.f;                     // torch.sum(mask == 1)
+            if (dmap) {
+                const float inv = 1.f / (B1 * B2);
+                const float dS_dmu1 = (2.f * mu2 * (A2 - A1) - S * 2.f * mu1 * (B2 - B1)) * inv;
+                const float dS_de11 = -S / B2;
+                const float dS_de12 = 2.f * A1 * inv;
+                const size_t o = (size_t)c * plane + idx;
+                dmap[o] = m * dS_dmu1;
+                dmap[(size_t)C * plane + o] = m * dS_de11;
+                dmap[2 * (size_t)C * plane + o] = m * dS_de12;
+            }
+        }
+    }
+    const size_t block = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    block_partials3(accS, accL, accN, red, partials + block * 3);
+}
+
+// one block: fixed-order reduction of the per-block partials in double
+// out[0] = ssim mean (1 if count == 0, loss_utils.py:48-49), out[1] = l1 mean (0 if count == 0, :29-30),
+// out[2] = count, out[3] = 1/count (0 if count == 0)
+__global__ void __launch_bounds__(256) loss_finalize_kernel(const float* __restrict__ partials, int nblocks,
+                                                            float* __restrict__ out) {
+    __shared__ double sh[3][256];
+    double a = 0, b = 0, c = 0;
+    for (int i = threadIdx.x; i < nblocks; i += 256) {
+        a += partials[3 * i];
+        b += partials[3 * i + 1];
+        c += partials[3 * i + 2];
+    }
+    sh[0][threadIdx.x] = a; sh[1][threadIdx.x] = b; sh[2][threadIdx.x] = c;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            sh[0][threadIdx.x] += sh[0][threadIdx.x + o];
+            sh[1][threadIdx.x] += sh[1][threadIdx.x + o];
+            sh[2][threadIdx.x] += sh[2][threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double n = sh[2][0];
+        out[0] = n > 0 ? (float)(sh[0][0] / n) : 1.f;
+        out[1] = n > 0 ? (float)(sh[1][0] / n) : 0.f;
+        out[2] = (float)n;
+        out[3] = n > 0 ? (float)(1.0 / n) : 0.f;
+    }
+}
+
+// ---- SSIM + masked L1 backward ------------------------------------------------------------------------
+// dL/dimg1 = kS * (conv(D0) + 2*img1*conv(D1) + img2*conv(D2)) + kL * sign(img1*m - img2*m) * m
+// with kS = coef[0]/count, kL = coef[1]/count (coef = upstream gradients of the two means, device scalars)
+__global__ void __launch_bounds__(IMG_THREADS) ssim_l1_backward_kernel(
+    int C, int H, int W, const float* __restrict__ img1, const float* __restrict__ img2,
+    const float* __restrict__ mask, size_t mask_cstride, Window win, const float* __restrict__ dmap,
+    const float* __restrict__ sums, const float* __restrict__ coef, float* __restrict__ dL_dimg1) {
+    __shared__ float sd[3][IMG_IN][IMG_IN + 1];
+    __shared__ float hs[3][IMG_IN][IMG_T];
+    const int tid = threadIdx.x, c = blockIdx.z;
+    const int x0 = blockIdx.x * IMG_T, y0 = blockIdx.y * IMG_T;
+    const size_t plane = (size_t)H * W;
+    for (int i = tid; i < IMG_IN * IMG_IN; i += IMG_THREADS) {
+        const int r = i / IMG_IN, q = i - r * IMG_IN;
+        const int y = y0 + r - HALO, x = x0 + q - HALO;
+        const bool in = (x >= 0) && (x < W) && (y >= 0) && (y < H);
+        const size_t o = (size_t)c * plane + (size_t)(in ? y : 0) * W + (in ? x : 0);
+#pragma unroll
+        for (int t = 0; t < 3; ++t) sd[t][r][q] = in ? dmap[(size_t)t * C * plane + o] : 0.f;
+    }
+    __syncthreads();
+    for (int i = tid; i < IMG_IN * IMG_T; i += IMG_THREADS) {
+        const int r = i >> 5, q = i & 31;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < WIN; ++k) {
+            const float w = win.w[k];
+            a0 = fmaf(w, sd[0][r][q + k], a0);
+            a1 = fmaf(w, sd[1][r][q + k], a1);
+            a2 = fmaf(w, sd[2][r][q + k], a2);
+        }
+        hs[0][r][q] = a0; hs[1][r][q] = a1; hs[2][r][q] = a2;
+    }
+    __syncthreads();
+    const int tx = tid & 31, ty = tid >> 5;
+    const float inv_n = sums[3];
+    const float kS = coef[0] * inv_n, kL = coef[1] * inv_n;
+#pragma unroll
+    for (int j = 0; j < IMG_T / IMG_WARPS; ++j) {
+        const int r = ty + IMG_WARPS * j;
+        const int y = y0 + r, x = x0 + tx;
+        float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < WIN; ++k) {
+            const float w = win.w[k];
+            c0 = fmaf(w, hs[0][r + k][tx], c0);
+            c1 = fmaf(w, hs[1][r + k][tx], c1);
+            c2 = fmaf(w, hs[2][r + k][tx], c2);
+        }
+        if (x < W && y < H) {
+            const size_t idx = (size_t)y * W + x;
+            const size_t o = (size_t)c * plane + idx;
+            const float a = img1[o], b = img2[o];
+            const float m = mask ? mask[(size_t)c * mask_cstride + idx] : 1.f;
+            const float d = a * m - b * m;
+            const float sgn = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
+            dL_dimg1[o] = kS * (c0 + 2.f * a * c1 + b * c2) + kL * sgn * m;
+        }
+    }
+}
+
+// ---- masked L1 (no SSIM): sum |x*m - t*m| and count(m == 1); target may be NULL (zeros) ---------------
+// complement != 0 uses m = 1 - mask (train.py:86: mask = 1 - sky_mask)
+__global__ void __launch_bounds__(IMG_THREADS) masked_l1_forward_kernel(
+    size_t n, size_t plane, const float* __restrict__ x, const float* __restrict__ target,
+    const float* __restrict__ mask, size_t mask_cstride, int complement, float* __restrict__ partials) {
+    __shared__ float red[3][IMG_WARPS];
+    float accL = 0.f, accN = 0.f;
+    for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < n; i += (size_t)gridDim.x * IMG_THREADS) {
+        float m = 1.f;
+        if (mask) {
+            const size_t c = i / plane;
+            m = mask[c * mask_cstride + (i - c * plane)];
+            if (complement) m = 1.f - m;
+        }
+        const float t = target ? target[i] : 0.f;
+        accL += fabsf(x[i] * m - t * m);
+        accN += (m == 1.f) ? 1.f : 0.f;
+    }
+    block_partials3(0.f, accL, accN, red, partials + (size_t)blockIdx.x * 3);
+}
+
+__global__ void __launch_bounds__(IMG_THREADS) masked_l1_backward_kernel(
+    size_t n, size_t plane, const float* __restrict__ x, const float* __restrict__ target,
+    const float* __restrict__ mask, size_t mask_cstride, int complement, const float* __restrict__ sums,
+    const float* __restrict__ coef, float* __restrict__ dL_dx) {
+    const float k = coef[0] * sums[3];
+    for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < n; i += (size_t)gridDim.x * IMG_THREADS) {
+        float m = 1.f;
+        if (mask) {
+            const size_t c = i / plane;
+            m = mask[c * mask_cstride + (i - c * plane)];
+            if (complement) m = 1.f - m;
+        }
+        const float t = target ? target[i] : 0.f;
+        const float d = x[i] * m - t * m;
+        const float sgn = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
+        dL_dx[i] = k * sgn * m;
+    }
+}
+
+// ---- depth_to_normal -------------------------------------------------------------------------------------
+// rays: device f32[21] = A (3x3 row-major, intrins.inverse().T), B (3x3 row-major, c2w[:3,:3].T), rays_o[3]:
+// rays_d = ([x, y, 1] @ A) @ B, points = depth * rays_d + rays_o (graphics_utils.py:146-155), evaluated in the
+// reference's two-step order so that the rounding of the points stays close to the torch graph's.
+constexpr int RAYS_N = 21;
+
+__device__ __forceinline__ float3 ray_dir(const float* M, int x, int y) {
+    const float fx = (float)x, fy = (float)y;
+    const float c0 = fmaf(fx, M[0], fmaf(fy, M[3], M[6]));
+    const float c1 = fmaf(fx, M[1], fmaf(fy, M[4], M[7]));
+    const float c2 = fmaf(fx, M[2], fmaf(fy, M[5], M[8]));
+    const float* B = M + 9;
+    return make_float3(fmaf(c0, B[0], fmaf(c1, B[3], c2 * B[6])), fmaf(c0, B[1], fmaf(c1, B[4], c2 * B[7])),
+                       fmaf(c0, B[2], fmaf(c1, B[5], c2 * B[8])));
+}
+__device__ __forceinline__ float3 cross3(const float3 a, const float3 b) {
+    return make_float3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__device__ __forceinline__ float dot3(const float3 a, const float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float3 world_point(const float* __restrict__ depth, const float* M, int W, int x, int y) {
+    const float d = depth[(size_t)y * W + x];
+    const float3 r = ray_dir(M, x, y);
+    const float* o = M + 18;
+    return make_float3(__fadd_rn(__fmul_rn(d, r.x), o[0]), __fadd_rn(__fmul_rn(d, r.y), o[1]),
+                       __fadd_rn(__fmul_rn(d, r.z), o[2]));
+}
+
+// dx / dy of graphics_utils.py:164-165 at an interior pixel: dx is the ROW difference, dy the COLUMN difference
+__device__ __forceinline__ void normal_diffs(const float* __restrict__ depth, const float* M, int W, int x, int y,
+                                             float3& dx, float3& dy) {
+    const float3 pu = world_point(depth, M, W, x, y + 1), pd = world_point(depth, M, W, x, y - 1);
+    const float3 pr = world_point(depth, M, W, x + 1, y), pl = world_point(depth, M, W, x - 1, y);
+    dx = make_float3(pu.x - pd.x, pu.y - pd.y, pu.z - pd.z);
+    dy = make_float3(pr.x - pl.x, pr.y - pl.y, pr.z - pl.z);
+}
+
+__global__ void __launch_bounds__(256) depth_to_normal_forward_kernel(int H, int W, const float* __restrict__ depth,
+                                                                      const float* __restrict__ rays,
+                                                                      float* __restrict__ normal /* [H,W,3] */) {
+    __shared__ float M[RAYS_N];
+    if (threadIdx.x < RAYS_N) M[threadIdx.x] = rays[threadIdx.x];
+    __syncthreads();
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= W || y >= H) return;
+    float3 n = make_float3(0.f, 0.f, 0.f);
+    if (x >= 1 && x < W - 1 && y >= 1 && y < H - 1) {
+        float3 dx, dy;
+        normal_diffs(depth, M, W, x, y, dx, dy);
+        const float3 v = cross3(dx, dy);
+        const float len = fmaxf(sqrtf(dot3(v, v)), 1e-12f);   // F.normalize eps
+        n = make_float3(v.x / len, v.y / len, v.z / len);
+    }
+    float* o = normal + ((size_t)y * W + x) * 3;
+    o[0] = n.x; o[1] = n.y; o[2] = n.z;
+}
+
+// gradient of the normal at interior pixel (cx, cy) w.r.t. its dx / dy vectors, given g = dL/dn there
+__device__ __forceinline__ void normal_backprop(const float* __restrict__ depth, const float* M,
+                                                const float* __restrict__ gn, int W, int cx, int cy, float3& g_dx,
+                                                float3& g_dy) {
+    float3 dx, dy;
+    normal_diffs(depth, M, W, cx, cy, dx, dy);
+    const float3 v = cross3(dx, dy);
+    const float len = sqrtf(dot3(v, v));
+    const float* gp = gn + ((size_t)cy * W + cx) * 3;
+    const float3 g = make_float3(gp[0], gp[1], gp[2]);
+    float3 u;
+    if (len > 1e-12f) {
+        const float inv = 1.f / len;
+        const float3 n = make_float3(v.x * inv, v.y * inv, v.z * inv);
+        const float ng = dot3(n, g);
+        u = make_float3((g.x - n.x * ng) * inv, (g.y - n.y * ng) * inv, (g.z - n.z * ng) * inv);
+    } else {
+        u = make_float3(g.x * 1e12f, g.y * 1e12f, g.z * 1e12f);   // clamp_min(eps) branch: v / eps
+    }
+    g_dx = cross3(dy, u);   // d(v.u)/d(dx), v = dx x dy
+    g_dy = cross3(u, dx);
+}
+
+__global__ void __launch_bounds__(256) depth_to_normal_backward_kernel(int H, int W, const float* __restrict__ depth,
+                                                                       const float* __restrict__ rays,
+                                                                       const float* __restrict__ dL_dnormal,
+                                                                       float* __restrict__ dL_ddepth) {
+    __shared__ float M[RAYS_N];
+    if (threadIdx.x < RAYS_N) M[threadIdx.x] = rays[threadIdx.x];
+    __syncthreads();
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= W || y >= H) return;
+    const float3 r = ray_dir(M, x, y);
+    float acc = 0.f;
+    float3 gdx, gdy;
+    auto interior = [&](int cx, int cy) { return cx >= 1 && cx < W - 1 && cy >= 1 && cy < H - 1; };
+    if (interior(x, y - 1)) { normal_backprop(depth, M, dL_dnormal, W, x, y - 1, gdx, gdy); acc += dot3(r, gdx); }
+    if (interior(x, y + 1)) { normal_backprop(depth, M, dL_dnormal, W, x, y + 1, gdx, gdy); acc -= dot3(r, gdx); }
+    if (interior(x - 1, y)) { normal_backprop(depth, M, dL_dnormal, W, x - 1, y, gdx, gdy); acc += dot3(r, gdy); }
+    if (interior(x + 1, y)) { normal_backprop(depth, M, dL_dnormal, W, x + 1, y, gdx, gdy); acc -= dot3(r, gdy); }
+    dL_ddepth[(size_t)y * W + x] = acc;
+}
+
+static inline int l1_blocks(size_t n) {
+    size_t b = (n + IMG_THREADS * 8 - 1) / (IMG_THREADS * 8);
+    const size_t cap = (size_t)NUM_SMS * 8;
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace r3dgw
+
+using namespace r3dgw;
+
+extern "C" {
+
+size_t r3dgw_image_loss_workspace_bytes(int C, int H, int W) {
+    if (C <= 0 || H <= 0 || W <= 0) return 256;
+    const size_t blocks = (size_t)((W + IMG_T - 1) / IMG_T) * ((H + IMG_T - 1) / IMG_T) * C;
+    const size_t l1b = (size_t)NUM_SMS * 8;
+    return align_up((blocks > l1b ? blocks : l1b) * 3 * sizeof(float), 256);
+}
+
+int r3dgw_ssim_l1_forward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                          size_t mask_channel_stride, float* dmap, char* workspace, float* out, void* stream_) {
+    if (C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !workspace || !out) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    dim3 grid((W + IMG_T - 1) / IMG_T, (H + IMG_T - 1) / IMG_T, C);
+    float* partials = reinterpret_cast<float*>(workspace);
+    {
+        ProfScope ps(KID_SSIM_FWD, stream);
+        ssim_l1_forward_kernel<<<grid, IMG_THREADS, 0, stream>>>(C, H, W, img1, img2, mask, mask_channel_stride,
+                                                                 make_window(), dmap, partials);
+    }
+    R3DGW_LAUNCH_CHECK();
+    loss_finalize_kernel<<<1, 256, 0, stream>>>(partials, (int)(grid.x * grid.y * grid.z), out);
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_ssim_l1_backward(int C, int H, int W, const float* img1, const float* img2, const float* mask,
+                           size_t mask_channel_stride, const float* dmap, const float* sums, const float* coef,
+                           float* dL_dimg1, void* stream_) {
+    if (C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !dmap || !sums || !coef || !dL_dimg1) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    dim3 grid((W + IMG_T - 1) / IMG_T, (H + IMG_T - 1) / IMG_T, C);
+    {
+        ProfScope ps(KID_SSIM_BWD, stream);
+        ssim_l1_backward_kernel<<<grid, IMG_THREADS, 0, stream>>>(C, H, W, img1, img2, mask, mask_channel_stride,
+                                                                  make_window(), dmap, sums, coef, dL_dimg1);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_masked_l1_forward(int C, int H, int W, const float* x, const float* target, const float* mask,
+                            size_t mask_channel_stride, int complement, char* workspace, float* out, void* stream_) {
+    if (C <= 0 || H <= 0 || W <= 0 || !x || !workspace || !out) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const size_t plane = (size_t)H * W, n = plane * C;
+    const int blocks = l1_blocks(n);
+    float* partials = reinterpret_cast<float*>(workspace);
+    {
+        ProfScope ps(KID_MASKED_L1, stream);
+        masked_l1_forward_kernel<<<blocks, IMG_THREADS, 0, stream>>>(n, plane, x, target, mask, mask_channel_stride,
+                                                                     complement, partials);
+    }
+    R3DGW_LAUNCH_CHECK();
+    loss_finalize_kernel<<<1, 256, 0, stream>>>(partials, blocks, out);
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_masked_l1_backward(int C, int H, int W, const float* x, const float* target, const float* mask,
+                             size_t mask_channel_stride, int complement, const float* sums, const float* coef,
+                             float* dL_dx, void* stream_) {
+    if (C <= 0 || H <= 0 || W <= 0 || !x || !sums || !coef || !dL_dx) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const size_t plane = (size_t)H * W, n = plane * C;
+    {
+        ProfScope ps(KID_MASKED_L1, stream);
+        masked_l1_backward_kernel<<<l1_blocks(n), IMG_THREADS, 0, stream>>>(n, plane, x, target, mask,
+                                                                           mask_channel_stride, complement, sums, coef,
+                                                                           dL_dx);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_depth_to_normal_forward(int H, int W, const float* depth, const float* rays, float* normal, void* stream_) {
+    if (H <= 0 || W <= 0 || !depth || !rays || !normal) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    dim3 grid((W + 31) / 32, (H + 7) / 8);
+    {
+        ProfScope ps(KID_DEPTH_NORMAL, stream);
+        depth_to_normal_forward_kernel<<<grid, 256, 0, stream>>>(H, W, depth, rays, normal);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_depth_to_normal_backward(int H, int W, const float* depth, const float* rays, const float* dL_dnormal,
+                                   float* dL_ddepth, void* stream_) {
+    if (H <= 0 || W <= 0 || !depth || !rays || !dL_dnormal || !dL_ddepth) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    dim3 grid((W + 31) / 32, (H + 7) / 8);
+    {
+        ProfScope ps(KID_DEPTH_NORMAL, stream);
+        depth_to_normal_backward_kernel<<<grid, 256, 0, stream>>>(H, W, depth, rays, dL_dnormal, dL_ddepth);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,190 @@
+"""Image-space post-ops of the training step over the C-ABI in include/r3dgw_b200.h.
+
+Drop-ins with the reference's names, signatures and edge-case behaviour (there is no CPU path):
+  l1_loss(network_output, gt, mask=None)                         utils/loss_utils.py:27-36
+  ssim(img1, img2, window_size=11, size_average=True, mask=None) utils/loss_utils.py:47-99
+  depth_to_normal(view, depth)                                   utils/graphics_utils.py:157-169
+and the fused form the training loop needs (train.py:78-81), one forward kernel + one backward kernel:
+  photometric_loss(image, gt, mask, lambda_dssim) -> (rec_loss, Ll1, Ssim)
+
+Difference from the reference, by design: `ssim` / `l1_loss` test `torch.sum(mask) == 0` on the host (a device
+sync per call) and return the Python constants 1 / 0; here the same values come back as device scalars with zero
+gradient, so the step never synchronises.
+"""
+import math
+
+import torch
+
+from . import native as _nat
+
+
+def _require_cuda(t, what):
+    if t.device.type != "cuda":
+        raise RuntimeError(f"{what} (B200-native): tensors must live on a CUDA device; there is no CPU path")
+
+
+def _f32c(t):
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _mask_args(mask, C, H, W):
+    """-> (tensor kept alive, data_ptr or None, channel stride in elements).  An expanded [C,H,W] view of a
+    [1,H,W] mask (viewpoint_cam.sky_mask.expand_as(gt_image), train.py:64-65) is passed with stride 0, not
+    materialised."""
+    if mask is None:
+        return None, None, 0
+    if mask.dim() == 2:
+        mask = mask.unsqueeze(0)
+    assert mask.shape[-2:] == (H, W), "the mask must be expanded as the input images"
+    if mask.shape[0] == 1 or (mask.stride(0) == 0):
+        m = _f32c(mask[0])
+        return m, m.data_ptr(), 0
+    assert mask.shape[0] == C, "the mask must be expanded as the input images"
+    m = _f32c(mask)
+    return m, m.data_ptr(), H * W
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+class _SsimL1Fn(torch.autograd.Function):
+    """(img1, img2, mask) -> (ssim mean over mask==1, masked L1 mean); gradient w.r.t. img1 only (gt has none)."""
+
+    @staticmethod
+    def forward(ctx, img1, img2, mask):
+        _require_cuda(img1, "ssim / l1_loss")
+        x, y = _f32c(img1), _f32c(img2)
+        if x.dim() == 4:
+            x, y = x.squeeze(0), y.squeeze(0)
+        C, H, W = (int(s) for s in x.shape)
+        mk, mptr, mstride = _mask_args(mask, C, H, W)
+        L = _nat.lib()
+        need_grad = ctx.needs_input_grad[0]
+        dmap = torch.empty(3, C, H, W, dtype=torch.float32, device=x.device) if need_grad else None
+        ws = torch.empty(L.r3dgw_image_loss_workspace_bytes(C, H, W), dtype=torch.uint8, device=x.device)
+        out = torch.empty(4, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            rc = L.r3dgw_ssim_l1_forward(C, H, W, x.data_ptr(), y.data_ptr(), mptr, mstride,
+                                         None if dmap is None else dmap.data_ptr(), ws.data_ptr(), out.data_ptr(),
+                                         _stream())
+        _nat.check(rc, "r3dgw_ssim_l1_forward")
+        ctx.keep = (x, y, mk, mptr, mstride, dmap, out)
+        ctx.in_shape = img1.shape
+        return out[0], out[1]
+
+    @staticmethod
+    def backward(ctx, g_ssim, g_l1):
+        x, y, mk, mptr, mstride, dmap, out = ctx.keep
+        C, H, W = (int(s) for s in x.shape)
+        coef = torch.stack([g_ssim.reshape(()).float(), g_l1.reshape(()).float()]).contiguous()
+        grad = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            rc = _nat.lib().r3dgw_ssim_l1_backward(C, H, W, x.data_ptr(), y.data_ptr(), mptr, mstride, dmap.data_ptr(),
+                                                   out.data_ptr(), coef.data_ptr(), grad.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_ssim_l1_backward")
+        return grad.reshape(ctx.in_shape), None, None
+
+
+class _MaskedL1Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_in, target, mask, complement):
+        _require_cuda(x_in, "l1_loss")
+        x = _f32c(x_in)
+        t = _f32c(target) if target is not None else None
+        xs = x.reshape(-1, x.shape[-2], x.shape[-1])
+        C, H, W = (int(s) for s in xs.shape)
+        mk, mptr, mstride = _mask_args(mask, C, H, W)
+        L = _nat.lib()
+        ws = torch.empty(L.r3dgw_image_loss_workspace_bytes(C, H, W), dtype=torch.uint8, device=x.device)
+        out = torch.empty(4, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            rc = L.r3dgw_masked_l1_forward(C, H, W, x.data_ptr(), None if t is None else t.data_ptr(), mptr, mstride,
+                                           int(bool(complement)), ws.data_ptr(), out.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_masked_l1_forward")
+        ctx.keep = (x, t, mk, mptr, mstride, out, int(bool(complement)), (C, H, W))
+        ctx.in_shape = x_in.shape
+        return out[1]
+
+    @staticmethod
+    def backward(ctx, g):
+        x, t, mk, mptr, mstride, out, complement, (C, H, W) = ctx.keep
+        coef = g.reshape(1).float().contiguous()
+        grad = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            rc = _nat.lib().r3dgw_masked_l1_backward(C, H, W, x.data_ptr(), None if t is None else t.data_ptr(), mptr,
+                                                     mstride, complement, out.data_ptr(), coef.data_ptr(),
+                                                     grad.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_masked_l1_backward")
+        return grad.reshape(ctx.in_shape), None, None, None
+
+
+def l1_loss(network_output, gt, mask=None, complement_mask=False):
+    """utils/loss_utils.py:27-36.  With a mask: sum|out*mask - gt*mask| / count(mask == 1) (0 when the mask is empty).
+    gt may be None (zeros, the sky-BRDF regulariser's torch.zeros_like target); complement_mask uses 1 - mask."""
+    return _MaskedL1Fn.apply(network_output, gt, mask, complement_mask)
+
+
+def ssim(img1, img2, window_size=11, size_average=True, mask=None):
+    """utils/loss_utils.py:47-99 (window 11, sigma 1.5, zero padding; mean of ssim_map*mask over count(mask == 1))."""
+    if window_size != 11 or not size_average:
+        raise NotImplementedError("fused ssim: window_size=11, size_average=True (the only form the reference calls)")
+    return _SsimL1Fn.apply(img1, img2, mask)[0]
+
+
+def photometric_loss(image, gt, mask, lambda_dssim):
+    """train.py:78-81 in one forward + one backward kernel: returns (rec_loss, Ll1, Ssim) with
+    Ssim = 1 - ssim(image, gt, mask) and rec_loss = Ll1*(1-lambda) + lambda*Ssim."""
+    s, l1 = _SsimL1Fn.apply(image, gt, mask)
+    d = 1.0 - s
+    return l1 * (1.0 - lambda_dssim) + lambda_dssim * d, l1, d
+
+
+# ---- depth_to_normal ----------------------------------------------------------------------------------------
+def ray_basis(view):
+    """The camera-constant part of depths_to_points (graphics_utils.py:142-155), computed with the same torch ops:
+    f32[21] = intrins.inverse().T (row-major), c2w[:3,:3].T (row-major), rays_o."""
+    wvt = view.world_view_transform
+    c2w = (wvt.T).inverse()
+    W, H = view.image_width, view.image_height
+    fx = W / (2 * math.tan(view.FoVx / 2.))
+    fy = H / (2 * math.tan(view.FoVy / 2.))
+    intrins = torch.tensor([[fx, 0., W / 2.], [0., fy, H / 2.], [0., 0., 1.0]], dtype=torch.float32, device=wvt.device)
+    return torch.cat([intrins.inverse().T.reshape(-1), c2w[:3, :3].T.reshape(-1), c2w[:3, 3].reshape(-1)]).contiguous()
+
+
+class _DepthToNormalFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, depth, rays):
+        _require_cuda(depth, "depth_to_normal")
+        d = _f32c(depth).reshape(depth.shape[-2], depth.shape[-1])
+        H, W = (int(s) for s in d.shape)
+        out = torch.empty(H, W, 3, dtype=torch.float32, device=d.device)
+        with torch.cuda.device(d.device):
+            rc = _nat.lib().r3dgw_depth_to_normal_forward(H, W, d.data_ptr(), rays.data_ptr(), out.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_depth_to_normal_forward")
+        ctx.keep = (d, rays)
+        ctx.in_shape = depth.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        d, rays = ctx.keep
+        H, W = (int(s) for s in d.shape)
+        g = _f32c(g)
+        grad = torch.empty_like(d)
+        with torch.cuda.device(d.device):
+            rc = _nat.lib().r3dgw_depth_to_normal_backward(H, W, d.data_ptr(), rays.data_ptr(), g.data_ptr(),
+                                                           grad.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_depth_to_normal_backward")
+        return grad.reshape(ctx.in_shape), None
+
+
+def depth_to_normal(view, depth, rays=None):
+    """utils/graphics_utils.py:157-169: depth [1,H,W] -> normal map [H,W,3] (zero on the 1-pixel border).
+    `rays` = ray_basis(view) may be passed in to reuse it across calls on the same camera."""
+    if rays is None:
+        rays = ray_basis(view)
+    return _DepthToNormalFn.apply(depth, rays.detach())

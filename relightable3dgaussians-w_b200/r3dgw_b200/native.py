@@ -12,7 +12,7 @@ PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(PKG_ROOT, "csrc")
 LIB_DIR = os.path.join(PKG_ROOT, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libr3dgw_b200.so")
-SOURCES = ["api.cu", "radix_sort.cu", "blend.cu", "knn.cu", "shade.cu"]
+SOURCES = ["api.cu", "radix_sort.cu", "blend.cu", "knn.cu", "shade.cu", "image_ops.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
@@ -24,7 +24,9 @@ SYMBOLS = [
     "r3dgw_geometry_backward", "r3dgw_rasterize_forward", "r3dgw_rasterize_backward",
     "r3dgw_mark_visible", "r3dgw_knn_workspace_bytes", "r3dgw_knn_dist2", "r3dgw_shade_forward",
     "r3dgw_shade_backward", "r3dgw_profile_enable", "r3dgw_profile_kernel_count", "r3dgw_profile_kernel_name",
-    "r3dgw_profile_read",
+    "r3dgw_profile_read", "r3dgw_image_loss_workspace_bytes", "r3dgw_ssim_l1_forward", "r3dgw_ssim_l1_backward",
+    "r3dgw_masked_l1_forward", "r3dgw_masked_l1_backward", "r3dgw_depth_to_normal_forward",
+    "r3dgw_depth_to_normal_backward",
 ]
 
 
@@ -140,6 +142,15 @@ def lib():
     sa = ctypes.POINTER(ShadeArgs)
     L.r3dgw_shade_forward.argtypes = [sa, vp, vp, vp, vp]
     L.r3dgw_shade_backward.argtypes = [sa] + [vp] * 11
+    sz = ctypes.c_size_t
+    L.r3dgw_image_loss_workspace_bytes.argtypes = [ci, ci, ci]
+    L.r3dgw_image_loss_workspace_bytes.restype = sz
+    L.r3dgw_ssim_l1_forward.argtypes = [ci, ci, ci, vp, vp, vp, sz, vp, vp, vp, vp]
+    L.r3dgw_ssim_l1_backward.argtypes = [ci, ci, ci, vp, vp, vp, sz, vp, vp, vp, vp, vp]
+    L.r3dgw_masked_l1_forward.argtypes = [ci, ci, ci, vp, vp, vp, sz, ci, vp, vp, vp]
+    L.r3dgw_masked_l1_backward.argtypes = [ci, ci, ci, vp, vp, vp, sz, ci, vp, vp, vp, vp]
+    L.r3dgw_depth_to_normal_forward.argtypes = [ci, ci, vp, vp, vp, vp]
+    L.r3dgw_depth_to_normal_backward.argtypes = [ci, ci, vp, vp, vp, vp, vp]
     L.r3dgw_profile_enable.argtypes = [ci]
     L.r3dgw_profile_enable.restype = None
     L.r3dgw_profile_kernel_name.argtypes = [ci]
@@ -148,7 +159,7 @@ def lib():
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name not in ("r3dgw_version", "r3dgw_launch_count", "r3dgw_knn_workspace_bytes", "r3dgw_profile_enable",
-                        "r3dgw_profile_kernel_name"):
+                        "r3dgw_profile_kernel_name", "r3dgw_image_loss_workspace_bytes"):
             fn.restype = ci
     _lib = L
     return L

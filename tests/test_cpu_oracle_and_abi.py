@@ -150,7 +150,7 @@ def test_product_path_never_imports_oracle():
     pkg = os.path.join(ROOT, "relightable3dgaussians-w_b200")
     for path in glob.glob(os.path.join(pkg, "**", "*.py"), recursive=True):
         src = open(path).read()
-        assert "raster_oracle" not in src and "shade_oracle" not in src and "ref_loader" not in src, path
+        assert all(w not in src for w in ("raster_oracle", "shade_oracle", "image_oracle", "ref_loader")), path
 
 
 def test_python_api_surface_and_errors():
@@ -171,3 +171,37 @@ def test_python_api_surface_and_errors():
     import simple_knn._C as knn
     with pytest.raises(RuntimeError, match="no CPU path"):
         knn.distCUDA2(x)
+
+
+# ---- image-space oracle vs the reference's own Python (fixtures from tests/golden/make_image_golden.py) ----
+def test_image_oracle_matches_reference_python():
+    import image_oracle as io
+    z = np.load(os.path.join(GOLD, "image_ops.npz"))
+    img, gt = torch.from_numpy(z["in_img"]), torch.from_numpy(z["in_gt"])
+    occl, sky = torch.from_numpy(z["in_occl"]), torch.from_numpy(z["in_sky"])
+    H, W = img.shape[-2:]
+    m3 = occl.expand(3, H, W)
+    x = img.clone().requires_grad_(True)
+    rec, l1, d = io.photometric(x, gt, m3, float(z["lam"]))
+    rec.backward()
+    np.testing.assert_allclose(l1.item(), z["ref_l1"], rtol=1e-6)
+    np.testing.assert_allclose(1.0 - d.item(), z["ref_ssim"], rtol=1e-6)
+    np.testing.assert_allclose(rec.item(), z["ref_rec"], rtol=1e-6)
+    np.testing.assert_allclose(x.grad.numpy(), z["ref_d_img"], rtol=1e-4, atol=1e-5 * np.abs(z["ref_d_img"]).max())
+    x = img.clone().requires_grad_(True)
+    lz = io.masked_l1(x, torch.zeros_like(x), 1 - sky.expand(3, H, W))
+    lz.backward()
+    np.testing.assert_allclose(lz.item(), z["ref_l1_sky"], rtol=1e-6)
+    np.testing.assert_allclose(x.grad.numpy(), z["ref_d_l1_sky"], rtol=1e-6, atol=0)
+    zero = torch.zeros(3, H, W)
+    assert io.masked_l1(img, gt, zero) == float(z["ref_l1_empty"]) == 0
+    assert io.ssim(img, gt, zero) == float(z["ref_ssim_empty"]) == 1
+    # depth_to_normal
+    depth = torch.from_numpy(z["in_depth"])
+    dm = (depth * sky).unsqueeze(0).clone().requires_grad_(True)
+    fovx, fovy = (float(v) for v in z["in_fov"])
+    n = io.depth_to_normal(torch.from_numpy(z["in_wvt"]), W, H, fovx, fovy, dm)
+    (n * torch.from_numpy(z["in_gn"])).sum().backward()
+    np.testing.assert_allclose(n.detach().numpy(), z["ref_normal"], rtol=0, atol=1e-6)
+    ref = z["ref_d_depth"]
+    np.testing.assert_allclose(dm.grad.numpy(), ref, rtol=1e-4, atol=1e-5 * np.abs(ref).max())
