@@ -3,9 +3,10 @@
 
 A STEP is one training iteration of the path on one view per GPU, driven through the reference's call pattern
 (r3dgw_b200.render.render == gaussian_renderer/__init__.py:69-274): fused relit shading of all Gaussians, 6 raster
-forwards on identical geometry (render, diffuse, specular, depth, normal, alpha), masked-L1-style loss against a GT
-image on 5 of them, backward through 5 raster backwards + geometry backward + shading backward (the post-15 000
-regime), and - for N > 1 - an NCCL all-reduce of the Gaussian-parameter gradients (views are sharded
+forwards on identical geometry (render, diffuse, specular, depth, normal, alpha), the image-space tail (normal
+compositing, depth_to_normal), the training loss of train.py:78-112 (masked L1 + SSIM against a GT image, sky-BRDF,
+normal-consistency, planar-scale and sky-depth regularisers), backward through 5 raster backwards + geometry
+backward + shading backward (the post-15 000 regime), and - for N > 1 - an NCCL all-reduce of the Gaussian-parameter gradients (views are sharded
 over ranks; weak scaling: one view per rank per step).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload B] [--mode dropin|fused]
@@ -29,7 +30,8 @@ for _p in (ROOT, PKG):
 
 METRIC = "train_iters_per_s_fwd+bwd_1M_gaussians_1080p"
 UNIT = "iters/s"
-LOSS_WEIGHTS = {"render": 1.0, "diffuse_color": 0.25, "specular_color": 0.25, "depth": 0.05, "normal": 0.1}
+# configs/optimizer/optimization_params.yaml:12-28 of the reference
+LAMBDA = {"dssim": 0.2, "sky_brdf": 0.5, "normal": 0.05, "scale": 100.0, "sky_gauss": 0.05}
 
 
 def parse_args():
@@ -142,10 +144,18 @@ class Stepper:
         self.sky_sh = sc.sky_sh.to(device).clone().requires_grad_(True)
         self.bg = torch.zeros(3, device=device)
         self.lut = make_lut(device)
+        H, W = int(cam.image_height), int(cam.image_width)
+        # masks all-ones except a 20 % top band of sky (sky_mask == 0 there); [H,W] / [1,H,W] like the
+        # reference's viewpoint_camera.sky_mask.squeeze() and occluders_mask
+        self.sky2 = torch.ones(H, W, device=device)
+        self.sky2[: H // 5] = 0
+        self.occl1 = torch.ones(1, H, W, device=device)
         if impl == "native":
             import diff_gaussian_rasterization as dgr
+            from r3dgw_b200 import image_ops
             self.raster = dgr
             self.shade_fn = R.fused_shade_fn(self.lut, 4)
+            self.ops = image_ops
         else:
             sys.path.insert(0, os.path.join(ROOT, "oracle"))
             import ref_loader
@@ -158,29 +168,79 @@ class Stepper:
                 return so.shade_all(env_sh, 4, lut, pc.means3D, normals, pc.albedo, pc.roughness, pc.metalness,
                                     pc.is_sky, cam_pos, sky_sh, specular, fix_sky)
             self.shade_fn = ref_shade
+            import image_oracle as io
+
+            class RefOps:
+                """the reference's torch graphs for the image-space ops (utils/loss_utils.py, graphics_utils.py),
+                restated in oracle/image_oracle.py - including their host-side `mask.sum() == 0` checks"""
+                l1_loss = staticmethod(lambda x, gt, mask=None: io.masked_l1(x, gt, mask))
+                ssim = staticmethod(lambda a, b, mask=None: io.ssim(a, b, mask))
+                depth_to_normal = staticmethod(lambda view, d: io.depth_to_normal(
+                    view.world_view_transform, int(view.image_width), int(view.image_height), view.FoVx, view.FoVy, d))
+            self.ops = RefOps
         self.params = self.pc.leaves() + [self.env_sh, self.sky_sh]
 
-    def forward(self, cam=None):
+    def forward(self, cam=None, sky_mask=None):
         cam = cam or self.cam
+        d2n = self.ops.depth_to_normal if sky_mask is not None else None
         if self.mode == "fused" and self.impl == "native":
-            return self.R.render_fused(cam, self.pc, self.env_sh, self.sky_sh, self.bg, self.shade_fn)
-        return self.R.render(cam, self.pc, self.env_sh, self.sky_sh, self.raster, self.bg, self.shade_fn)
+            return self.R.render_fused(cam, self.pc, self.env_sh, self.sky_sh, self.bg, self.shade_fn,
+                                       sky_mask=sky_mask, depth_to_normal=d2n)
+        return self.R.render(cam, self.pc, self.env_sh, self.sky_sh, self.raster, self.bg, self.shade_fn,
+                             sky_mask=sky_mask, depth_to_normal=d2n)
 
-    def loss(self, out, gt):
-        loss = 0.0
-        for k, w in LOSS_WEIGHTS.items():
-            loss = loss + w * (out[k] - gt).abs().mean()
-        return loss
+    def loss(self, out, gt, cam, sky2, occl1):
+        """train.py:78-112 in the post-15 000 regime: photometric (masked L1 + SSIM), sky-BRDF, normal-consistency,
+        planar-scale and sky-depth regularisers (the env-SH positivity term, train.py:99-102, samples 10 random
+        directions on a [10,25,3] tensor - negligible and stochastic - and is left out of both arms)."""
+        torch, ops, pc = self.torch, self.ops, self.pc
+        gt3 = gt
+        occl3, sky3 = occl1.expand_as(gt3), sky2.unsqueeze(0).expand_as(gt3)
+        if self.mode == "fused" and self.impl == "native":
+            loss = ops.photometric_loss(out["render"], gt3, occl3, LAMBDA["dssim"])[0]
+            loss_sky = ops.l1_loss(out["diffuse_color"], None, mask=sky2, complement_mask=True) + \
+                ops.l1_loss(out["specular_color"], None, mask=sky2, complement_mask=True)
+        else:
+            Ll1 = ops.l1_loss(out["render"], gt3, mask=occl3)
+            Ssim = 1.0 - ops.ssim(out["render"], gt3, mask=occl3)
+            loss = Ll1 * (1 - LAMBDA["dssim"]) + LAMBDA["dssim"] * Ssim
+            loss_sky = ops.l1_loss(out["diffuse_color"], torch.zeros_like(out["diffuse_color"]), mask=1 - sky3) + \
+                ops.l1_loss(out["specular_color"], torch.zeros_like(out["specular_color"]), mask=1 - sky3)
+        loss = loss + LAMBDA["sky_brdf"] * loss_sky
+        rn = out["normal"] * occl3 * sky3
+        rs = out["normal_ref"] * occl3 * sky3
+        loss = loss + LAMBDA["normal"] * (1 - (rn * rs).sum(dim=0))[None].mean()
+        # min_scale_loss (loss_utils.py:181-191) and depth_loss_gaussians (:139-147): caller-side torch on [P] arrays
+        vis = out["radii"] > 0
+        is_sky = pc.is_sky.reshape(-1)
+        wvt = cam.world_view_transform
+        depth = pc.means3D @ wvt[:3, 2:3] + wvt[3, 2]
+        if self.mode == "fused" and self.impl == "native":
+            # same values without boolean-mask indexing (no device->host sync)
+            fg = (vis & ~is_sky).float()
+            loss = loss + LAMBDA["scale"] * (pc.scales.min(dim=-1)[0] * fg).sum() / fg.sum().clamp_min(1.0)
+            sk = (vis & is_sky).float().unsqueeze(1)
+            avg_sky = (depth * sk).sum() / sk.sum().clamp_min(1.0)
+            avg_non = ((depth * fg.unsqueeze(1)).sum() / fg.sum().clamp_min(1.0)).detach()
+        else:
+            if vis.sum() > 0:
+                sc = pc.scales[vis & ~is_sky]
+                loss = loss + LAMBDA["scale"] * torch.sort(sc, dim=-1)[0][..., 0].mean()
+            avg_sky = torch.mean(depth[is_sky & vis])
+            avg_non = torch.mean(depth[(~is_sky) & vis]).detach()
+        return loss + LAMBDA["sky_gauss"] * torch.exp(-0.02 * (avg_sky - avg_non))
 
-    def step(self, gt, cam=None):
+    def step(self, gt, cam=None, sky2=None, occl1=None):
         # optimizer-style in-place touch of every parameter (x *= 1): bumps the tensors' version counters exactly as
         # an optimizer step does, so nothing computed for the previous iteration (geometry cache) can be reused
         with self.torch.no_grad():
             self.torch._foreach_mul_(self.params, 1.0)
         for p in self.params:
             p.grad = None
-        out = self.forward(cam)
-        loss = self.loss(out, gt)
+        sky2 = self.sky2 if sky2 is None else sky2
+        occl1 = self.occl1 if occl1 is None else occl1
+        out = self.forward(cam, sky2)
+        loss = self.loss(out, gt, cam or self.cam, sky2, occl1)
         loss.backward()
         return loss
 
@@ -233,6 +293,10 @@ def algorithmic_bytes(kernel, P, Pv, R, N, tiles, C, n_pass):
         "geometry_backward": 160 * Pv,
         "shade_forward": 80 * P,
         "shade_backward": 100 * P,
+        "ssim_l1_forward": (2 * 4 * C + 4 + 3 * 4 * C) * N,                     # img, gt, mask in; 3 derivative maps out
+        "ssim_l1_backward": (3 * 4 * C + 2 * 4 * C + 4 + 4 * C) * N,            # 3 maps, img, gt, mask in; grad out
+        "masked_l1": (4 * C + 4) * N,
+        "depth_to_normal": 16 * N,
     }
     return table.get(kernel)
 
@@ -372,7 +436,10 @@ def main():
     d_view, d_proj = torch.empty(4, 4, device=device), torch.empty(4, 4, device=device)
     d_cpos = torch.empty(3, device=device)
     h_loss = torch.zeros(1).pin_memory()
-    h2d = sum(t.numel() * t.element_size() for t in (h_gt, h_view, h_proj, h_cpos, h_env, h_sky))
+    # per-view masks travel as 8-bit images too (viewpoint_cam.sky_mask / occluders_mask, train.py:64-65)
+    h_skym, h_occl = pin(st.sky2.cpu().to(torch.uint8)), pin(st.occl1.cpu().to(torch.uint8))
+    d_skym8, d_occl8 = torch.empty_like(st.sky2, dtype=torch.uint8), torch.empty_like(st.occl1, dtype=torch.uint8)
+    h2d = sum(t.numel() * t.element_size() for t in (h_gt, h_view, h_proj, h_cpos, h_env, h_sky, h_skym, h_occl))
     # measured pinned H2D bandwidth of this box (reported beside e2e: some hosts deliver a fraction of PCIe 5)
     probe_h = torch.empty(64 << 20, dtype=torch.uint8).pin_memory()
     probe_d = torch.empty(64 << 20, dtype=torch.uint8, device=device)
@@ -392,7 +459,9 @@ def main():
             st.env_sh.copy_(h_env, non_blocking=True)
             st.sky_sh.copy_(h_sky, non_blocking=True)
         c = Camera(W, H, cam.FoVx, cam.FoVy, d_view, d_proj, d_cpos)
-        loss = st.step(d_gt, c)
+        d_skym8.copy_(h_skym, non_blocking=True)
+        d_occl8.copy_(h_occl, non_blocking=True)
+        loss = st.step(d_gt, c, d_skym8.to(torch.float32), d_occl8.to(torch.float32))
         if bucket is not None:
             bucket.all_reduce(average_over=world)
         h_loss.copy_(loss.detach().reshape(1), non_blocking=True)
@@ -407,7 +476,8 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {P} Gaussians, {W}x{H}, 1 view/GPU/step, shade + 6 raster fwd + "
-                                   f"5 raster bwd ({args.mode})", "l2": "512 MiB flush between timed steps",
+                                   f"5 raster bwd + masked L1/SSIM, sky-BRDF, normal (depth_to_normal), scale and sky-depth "
+                                   f"regularisers as train.py:74-116 ({args.mode})", "l2": "512 MiB flush between timed steps",
                        "mode": args.mode, "views_per_step": world},
             "clocks": clocks, "gpu_launches": int(gpu_launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
@@ -426,7 +496,7 @@ def main():
         if new_view and args.impl == "native":
             st.raster.clear_geometry_cache()     # a new view every frame: nothing carried over
         with torch.no_grad():
-            st.forward()
+            st.forward(None, st.sky2)
     nf = max(5, args.steps // 2)
     scale_n = world if args.impl == "native" else 1
     line["fps_fwd"] = scale_n * 1e3 / (timed_steps(torch, frame, nf, 2, flush, dist) / nf)

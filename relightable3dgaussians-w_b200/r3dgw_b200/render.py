@@ -73,10 +73,24 @@ def _prepare(camera, pc, env_sh, sky_sh, shade_fn, specular, fix_sky):
     return colors, diffuse, spec, depth, 0.5 * normals + 0.5
 
 
+def image_post_ops(out, camera, sky_mask, depth_to_normal):
+    """The image-space tail of the reference's render() (gaussian_renderer/__init__.py:233-237, 266-272), same torch
+    expressions: the rendered normal composited over the sky, and `normal_ref` from the masked depth map.
+    `depth_to_normal(view, depth[1,H,W]) -> [H,W,3]` is the reference's function or its drop-in.
+    (normalize_normal_inplace, :54-57, rebinds a local and has no effect; it is not mirrored.)"""
+    n = out["normal"]
+    out["normal"] = n * sky_mask + torch.ones_like(n) * (1 - sky_mask)
+    nref = depth_to_normal(camera, (out["depth"][0] * sky_mask).unsqueeze(0)).permute(2, 0, 1)
+    nref = nref * out["alpha"].detach()
+    out["normal_ref"] = nref + torch.ones_like(nref) * (1 - sky_mask)
+    return out
+
+
 def render(camera, pc, env_sh, sky_sh, raster, bg_color, shade_fn, scaling_modifier=1.0, debug=False, specular=True,
-           fix_sky=False):
-    """Same raster-call sequence as the reference's render(); returns its dict (without the image-space post-ops
-    depth_to_normal / normalize_normal_inplace)."""
+           fix_sky=False, sky_mask=None, depth_to_normal=None):
+    """Same raster-call sequence as the reference's render(); returns its dict.  With `sky_mask` [H,W] and a
+    `depth_to_normal` callable the image-space tail (normal compositing, normal_ref) is appended as in the
+    reference."""
     means3D = pc.means3D
     screenspace_points = torch.zeros_like(means3D, requires_grad=True) + 0
     try:
@@ -121,10 +135,13 @@ def render(camera, pc, env_sh, sky_sh, raster, bg_color, shade_fn, scaling_modif
         out[k] = img
     rasterizer_alpha = raster.GaussianRasterizer(raster_settings=settings(torch.zeros(3, device=means3D.device)))
     out["alpha"] = call(rasterizer_alpha, torch.ones_like(means3D))[0]
+    if sky_mask is not None and depth_to_normal is not None:
+        image_post_ops(out, camera, sky_mask, depth_to_normal)
     return out
 
 
-def render_fused(camera, pc, env_sh, sky_sh, bg_color, shade_fn, scaling_modifier=1.0, specular=True, fix_sky=False):
+def render_fused(camera, pc, env_sh, sky_sh, bg_color, shade_fn, scaling_modifier=1.0, specular=True, fix_sky=False,
+                 sky_mask=None, depth_to_normal=None):
     """One geometry pass + ONE 16-channel blend (render 3, diffuse 3, specular 3, depth 3, normal 3, alpha 1) instead
     of six 3-channel raster calls.  Returns the same keys as render(debug=False)."""
     import diff_gaussian_rasterization as dgr
@@ -144,6 +161,9 @@ def render_fused(camera, pc, env_sh, sky_sh, bg_color, shade_fn, scaling_modifie
     bg16 = torch.cat([bg_color.reshape(3).repeat(5), torch.zeros(1, device=means3D.device)])
     img, radii = dgr.rasterize_gaussians_features(means3D, screenspace_points, feats, pc.opacity, pc.scales,
                                                   pc.rotations, None, s, bg=bg16)
-    return {"render": img[0:3], "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii,
-            "diffuse_color": img[3:6], "specular_color": img[6:9], "depth": img[9:12],
-            "normal": (img[12:15] - 0.5) * 2.0, "alpha": img[15:16].expand(3, -1, -1)}
+    out = {"render": img[0:3], "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii,
+           "diffuse_color": img[3:6], "specular_color": img[6:9], "depth": img[9:12],
+           "normal": (img[12:15] - 0.5) * 2.0, "alpha": img[15:16].expand(3, -1, -1)}
+    if sky_mask is not None and depth_to_normal is not None:
+        image_post_ops(out, camera, sky_mask, depth_to_normal)
+    return out
