@@ -128,6 +128,24 @@ int r3dgw_blend_forward(
     float* out_color,        /* f32[C,H,W] */
     void* stream);
 
+/* K4 with an alpha cache, for repeated blends over ONE geometry (the six raster calls of render(),
+ * gaussian_renderer/__init__.py:160-264; one view x many environment maps in the relit-eval grid).
+ *   cache_mode 0: plain K4 (alpha_cache ignored) == r3dgw_blend_forward
+ *   cache_mode 1: plain K4 that also records, per (sorted list entry, 8x4-pixel warp footprint) that survives the
+ *                 footprint cull, the 32 pixels' effective alphas (0 = did not blend) into alpha_cache
+ *   cache_mode 2: replays alpha_cache instead of re-evaluating conic / exp / thresholds; image_buffer must be
+ *                 the one a mode-0/1 call on the same geometry filled (final_T, n_contrib are read, not written).
+ * Output is bit-identical in all three modes.  alpha_cache: r3dgw_alpha_cache_bytes(R) bytes (R * 1 KiB, only the
+ * surviving rows are ever touched), caller-owned device memory. */
+size_t r3dgw_alpha_cache_bytes(int R);
+int r3dgw_blend_forward_cached(
+    int P, int R, int C,
+    const r3dgw_camera* cam,
+    const char* geom_buffer, const char* binning_buffer, char* image_buffer,
+    const float* features, const float* background, float* out_color,
+    float* alpha_cache, int cache_mode,
+    void* stream);
+
 /* K5: backward of the blend; ACCUMULATES (+=) into dL_dmean2D[P,3], dL_dconic[P,4],
  * dL_dopacity[P], dL_dfeatures[P,C] (caller zeroes them).  Reference: backward.cu:399-557. */
 int r3dgw_blend_backward(

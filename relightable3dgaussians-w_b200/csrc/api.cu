@@ -25,7 +25,7 @@ uint64_t g_prof_n[KID_COUNT] = {0};
 const char* const g_prof_names[KID_COUNT] = {
     "preprocess_scan", "duplicate_keys", "sort_histogram", "sort_scan", "sort_onesweep_pass", "ranges_gather",
     "blend_forward", "blend_backward", "geometry_backward", "shade_forward", "shade_backward", "knn", "mark_visible",
-    "ssim_l1_forward", "ssim_l1_backward", "masked_l1", "depth_to_normal"};
+    "ssim_l1_forward", "ssim_l1_backward", "masked_l1", "depth_to_normal", "blend_forward_cached"};
 cudaEvent_t prof_event() {
     if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
     cudaEvent_t e; cudaEventCreate(&e); return e;
@@ -45,7 +45,7 @@ void prof_mark(int id, cudaStream_t s, bool end) {
 
 int blend_forward_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
                            const float* features, const float* bg, float* final_T, uint32_t* n_contrib,
-                           float* out_color, cudaStream_t stream);
+                           float* out_color, float* alpha_cache, int cache_mode, cudaStream_t stream);
 int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
                             const float* bg, const float* features, const float* final_T,
                             const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
@@ -253,10 +253,14 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
     return 0;
 }
 
-int r3dgw_blend_forward(int P, int R, int C, const r3dgw_camera* cam, const char* geom_buffer,
-                        const char* binning_buffer, char* image_buffer, const float* features,
-                        const float* background, float* out_color, void* stream_) {
+size_t r3dgw_alpha_cache_bytes(int R) { return R > 0 ? (size_t)R * TILE_PIX * sizeof(float) : 0; }
+
+int r3dgw_blend_forward_cached(int P, int R, int C, const r3dgw_camera* cam, const char* geom_buffer,
+                               const char* binning_buffer, char* image_buffer, const float* features,
+                               const float* background, float* out_color, float* alpha_cache, int cache_mode,
+                               void* stream_) {
     if (!cam || !binning_buffer || !image_buffer || !background || !out_color || R < 0 || P < 0) return R3DGW_ERR_BAD_ARG;
+    if (cache_mode < 0 || cache_mode > 2 || (cache_mode != 0 && !alpha_cache && R > 0)) return R3DGW_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
     const int W = cam->width, H = cam->height;
     r3dgw_binning_layout BL; binning_layout(R, W, H, &BL);
@@ -270,7 +274,14 @@ int r3dgw_blend_forward(int P, int R, int C, const r3dgw_camera* cam, const char
     const float4* A = (const float4*)(binning_buffer + BL.splats);
     return blend_forward_dispatch(C, grid, (const uint2*)(binning_buffer + BL.ranges), A, A + R, W, H, features,
                                   background, (float*)(image_buffer + IL.final_T),
-                                  (uint32_t*)(image_buffer + IL.n_contrib), out_color, stream);
+                                  (uint32_t*)(image_buffer + IL.n_contrib), out_color, alpha_cache, cache_mode, stream);
+}
+
+int r3dgw_blend_forward(int P, int R, int C, const r3dgw_camera* cam, const char* geom_buffer,
+                        const char* binning_buffer, char* image_buffer, const float* features,
+                        const float* background, float* out_color, void* stream_) {
+    return r3dgw_blend_forward_cached(P, R, C, cam, geom_buffer, binning_buffer, image_buffer, features, background,
+                                      out_color, nullptr, 0, stream_);
 }
 
 int r3dgw_blend_backward(int P, int R, int C, const r3dgw_camera* cam, const char* geom_buffer,

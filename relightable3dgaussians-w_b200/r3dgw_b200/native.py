@@ -26,7 +26,7 @@ SYMBOLS = [
     "r3dgw_shade_backward", "r3dgw_profile_enable", "r3dgw_profile_kernel_count", "r3dgw_profile_kernel_name",
     "r3dgw_profile_read", "r3dgw_image_loss_workspace_bytes", "r3dgw_ssim_l1_forward", "r3dgw_ssim_l1_backward",
     "r3dgw_masked_l1_forward", "r3dgw_masked_l1_backward", "r3dgw_depth_to_normal_forward",
-    "r3dgw_depth_to_normal_backward",
+    "r3dgw_depth_to_normal_backward", "r3dgw_alpha_cache_bytes", "r3dgw_blend_forward_cached",
 ]
 
 
@@ -130,6 +130,9 @@ def lib():
     L.r3dgw_geometry_forward.argtypes = [ALLOC_FN, vp, ALLOC_FN, vp, ci, ci, ci, cam,
                                          vp, vp, vp, vp, vp, vp, vp, ctypes.POINTER(ci), vp]
     L.r3dgw_blend_forward.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp]
+    L.r3dgw_blend_forward_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp, ci, vp]
+    L.r3dgw_alpha_cache_bytes.argtypes = [ci]
+    L.r3dgw_alpha_cache_bytes.restype = ctypes.c_size_t
     L.r3dgw_blend_backward.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     L.r3dgw_geometry_backward.argtypes = [ci, ci, ci, cam] + [vp] * 16
     L.r3dgw_rasterize_forward.argtypes = [ALLOC_FN, vp, ALLOC_FN, vp, ALLOC_FN, vp, ci, ci, ci, vp, cam,
@@ -159,7 +162,7 @@ def lib():
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name not in ("r3dgw_version", "r3dgw_launch_count", "r3dgw_knn_workspace_bytes", "r3dgw_profile_enable",
-                        "r3dgw_profile_kernel_name", "r3dgw_image_loss_workspace_bytes"):
+                        "r3dgw_profile_kernel_name", "r3dgw_image_loss_workspace_bytes", "r3dgw_alpha_cache_bytes"):
             fn.restype = ci
     _lib = L
     return L

@@ -485,3 +485,47 @@ def test_relit_grid_geometry_reuse_is_exact(native_lib):
         R.render(sc.camera, pc, envs[0], sc.sky_sh, dgr, bg, shade)
         assert dgr.last_geometry_state() is not st1
     assert st_cached is not None
+
+
+@pytest.mark.parametrize("name,kw", [("small", {}), ("small", dict(W=333, H=211, seed_offset=5)), ("A", {})])
+def test_alpha_cache_replay_is_bit_exact(native_lib, name, kw):
+    """Blends #2 (records the alphas) and #3.. (replay them from HBM) over one geometry must produce exactly the image
+    and - through the shared final_T / n_contrib - exactly-as-good gradients as the plain kernel, for different channel
+    counts and backgrounds, and the replay kernel must actually have run."""
+    import diff_gaussian_rasterization as dgr
+    from r3dgw_b200 import native
+    from r3dgw_b200.synthetic import make_scene
+    sc = make_scene(name, **kw).to("cuda")
+    s = _settings(dgr, sc)
+    g = torch.Generator().manual_seed(17)
+    feats = [torch.rand(sc.P, c, generator=g).cuda() for c in (3, 3, 3, 16, 1, 3)]
+    bgs = [torch.rand(f.shape[1], generator=g).cuda() for f in feats]
+    ups = [(torch.randn(f.shape[1], s.image_height, s.image_width, generator=g) * 1e-3).cuda() for f in feats]
+
+    def run(alpha_cache):
+        dgr.set_alpha_cache(alpha_cache)
+        m3 = sc.means3D.clone().requires_grad_(True)
+        op = sc.opacities.clone().requires_grad_(True)
+        m2 = torch.zeros_like(m3, requires_grad=True)
+        fl = [f.clone().requires_grad_(True) for f in feats]
+        imgs = [dgr.rasterize_gaussians_features(m3, m2, f, op, sc.scales, sc.rotations, None, s, bg=b)[0]
+                for f, b in zip(fl, bgs)]
+        st = dgr.last_geometry_state()
+        sum((i * u).sum() for i, u in zip(imgs, ups)).backward()
+        return [i.detach() for i in imgs], [f.grad for f in fl] + [m3.grad, op.grad], st
+
+    native.profile_read(reset=True)
+    native.profile_enable(True)
+    on_imgs, on_grads, st = run(True)
+    torch.cuda.synchronize()
+    prof = native.profile_read(reset=True)
+    native.profile_enable(False)
+    assert st.alpha_cache is not None and st.blend_calls == len(feats)
+    assert prof["blend_forward_cached"][1] == len(feats) - 2 and prof["blend_forward"][1] == 2
+    off_imgs, off_grads, st_off = run(False)
+    dgr.set_alpha_cache(True)
+    assert st_off.alpha_cache is None
+    for k, (a, b) in enumerate(zip(on_imgs, off_imgs)):
+        assert torch.equal(a, b), f"blend #{k + 1}"
+    for k, (a, b) in enumerate(zip(on_grads, off_grads)):   # same kernels, same inputs: only atomic order differs
+        _grad_close(a, b, f"grad[{k}]")
