@@ -106,8 +106,12 @@ class GeometryState:
         self.handles = None       # autograd handles (h_mean2D, h_conic, h_opacity, h_rgb)
         # alpha cache (see _BlendFn): filled by the SECOND blend over this geometry, replayed by every later one
         self.blend_calls = 0
-        self.alpha_cache = None
         self.alpha_img = None     # image buffer (final_T, n_contrib) of the pass that filled the cache
+
+    @property
+    def alpha_cache(self):
+        """The recorded alphas, if this state still owns the process-wide pool buffer."""
+        return _alpha_pool["buf"] if (self.alpha_img is not None and _alpha_pool["owner"] is self) else None
 
     # ---- views into the opaque buffers (tests / tooling) -------------------------------------
     def _geom_layout(self):
@@ -254,18 +258,14 @@ class _BlendFn(torch.autograd.Function):
         # render(), or a relit-eval grid re-shading one view per environment map - replays them, bit-identically.
         st.blend_calls += 1
         mode, cache = 0, None
-        if st.alpha_cache is not None:
-            mode, cache, img = 2, st.alpha_cache, st.alpha_img
+        if st.alpha_img is not None and _alpha_pool["owner"] is st:
+            mode, cache, img = 2, _alpha_pool["buf"], st.alpha_img
         else:
             img = torch.empty(IL.total, dtype=torch.uint8, device=dev)
             if _ALPHA_CACHE and st.blend_calls >= 2 and st.R > 0:
-                nbytes = int(L.r3dgw_alpha_cache_bytes(st.R))
-                if nbytes <= _ALPHA_CACHE_BYTES:
-                    try:   # rounded up so that step-to-step changes of R keep hitting the same cached block
-                        cache = torch.empty(-(-nbytes // _ALPHA_ROUND) * _ALPHA_ROUND, dtype=torch.uint8, device=dev)
-                        mode = 1
-                    except torch.OutOfMemoryError:
-                        cache = None
+                cache = _alpha_pool_get(int(L.r3dgw_alpha_cache_bytes(st.R)), dev)
+                if cache is not None:
+                    mode = 1
         with torch.cuda.device(dev):
             rc = L.r3dgw_blend_forward_cached(st.P, st.R, C, ctypes.byref(st.cam), st.geom.data_ptr(),
                                               st.binning.data_ptr(), img.data_ptr(), _ptr(feats), bgc.data_ptr(),
@@ -273,7 +273,7 @@ class _BlendFn(torch.autograd.Function):
                                               _stream())
         _nat.check(rc, "r3dgw_blend_forward_cached")
         if mode == 1:
-            st.alpha_cache, st.alpha_img = cache, img
+            _alpha_pool["owner"], st.alpha_img = st, img
         ctx.st, ctx.C, ctx.use_sh = st, C, use_sh
         ctx.means2D_shape = means2D.shape
         ctx.feat_shape = features.shape
@@ -315,10 +315,37 @@ _ALPHA_CACHE_BYTES = int(float(os.environ.get("R3DGW_ALPHA_CACHE_GB", "24")) * (
 _ALPHA_ROUND = 256 << 20
 
 
+# One grow-only device buffer serves every geometry state in turn (the state that recorded last owns it): a fresh
+# multi-GB cudaMalloc per view costs tens of ms of page-table setup, and R moves a little every training step.
+_alpha_pool = {"buf": None, "owner": None}
+
+
+def _alpha_pool_get(nbytes, device):
+    if nbytes > _ALPHA_CACHE_BYTES:
+        return None
+    buf = _alpha_pool["buf"]
+    if buf is None or buf.device != device or buf.numel() < nbytes:
+        _alpha_pool["buf"], _alpha_pool["owner"] = None, None
+        del buf
+        want = min(max(-(-(nbytes + nbytes // 4) // _ALPHA_ROUND) * _ALPHA_ROUND, nbytes), max(_ALPHA_CACHE_BYTES, nbytes))
+        for size in (want, nbytes):
+            try:
+                _alpha_pool["buf"] = torch.empty(size, dtype=torch.uint8, device=device)
+                break
+            except torch.OutOfMemoryError:
+                torch.cuda.empty_cache()
+        if _alpha_pool["buf"] is None:
+            return None
+    _alpha_pool["owner"] = None      # the caller records next and takes ownership
+    return _alpha_pool["buf"]
+
+
 def set_alpha_cache(enabled: bool):
     global _ALPHA_CACHE
     _ALPHA_CACHE = bool(enabled)
     clear_geometry_cache()
+    if not enabled:
+        _alpha_pool["buf"], _alpha_pool["owner"] = None, None
 
 
 _cache = {"key": None, "entry": None}
