@@ -147,7 +147,8 @@ int r3dgw_blend_forward_cached(
     void* stream);
 
 /* K5: backward of the blend; ACCUMULATES (+=) into dL_dmean2D[P,3], dL_dconic[P,4],
- * dL_dopacity[P], dL_dfeatures[P,C] (caller zeroes them).  Reference: backward.cu:399-557. */
+ * dL_dopacity[P], dL_dfeatures[P,C] (caller zeroes them).  Reference: backward.cu:399-557.
+ * dL_dfeatures may be NULL: geometry-only pass (see r3dgw_blend_backward_color_cached). */
 int r3dgw_blend_backward(
     int P, int R, int C,
     const r3dgw_camera* cam,
@@ -155,6 +156,22 @@ int r3dgw_blend_backward(
     const float* features, const float* background,
     const float* dL_dpixels,  /* f32[C,H,W] */
     float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dfeatures,
+    void* stream);
+
+/* Deferred backward for repeated blends over one geometry (the 5-6 raster backwards of one render()):
+ *   per call   r3dgw_blend_backward_color_cached : dL/dfeatures[P,C] (+=) only, replayed front to back from the alpha
+ *              cache a mode-1 r3dgw_blend_forward_cached call recorded (C <= 4);
+ *   once       r3dgw_blend_backward with dL_dfeatures == NULL over the CONCATENATED features [P, sum C], background
+ *              [sum C] and pixel gradients [sum C, H, W] of all calls: the geometry gradients (mean2D, conic, opacity)
+ *              of the whole frame in one walk of the tile lists instead of one per call.
+ * The sums are the ones the reference accumulates call by call (backward.cu:399-557); only the atomic order differs. */
+int r3dgw_blend_backward_color_cached(
+    int P, int R, int C,
+    const r3dgw_camera* cam,
+    const char* binning_buffer, const char* image_buffer,
+    const float* alpha_cache,
+    const float* dL_dpixels,   /* f32[C,H,W] */
+    float* dL_dfeatures,       /* f32[P,C], accumulated */
     void* stream);
 
 /* K6+K7 fused: conic/mean2D gradients -> means3D, cov3D, scales, rotations (and SH).

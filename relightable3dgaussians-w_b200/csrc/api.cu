@@ -25,7 +25,8 @@ uint64_t g_prof_n[KID_COUNT] = {0};
 const char* const g_prof_names[KID_COUNT] = {
     "preprocess_scan", "duplicate_keys", "sort_histogram", "sort_scan", "sort_onesweep_pass", "ranges_gather",
     "blend_forward", "blend_backward", "geometry_backward", "shade_forward", "shade_backward", "knn", "mark_visible",
-    "ssim_l1_forward", "ssim_l1_backward", "masked_l1", "depth_to_normal", "blend_forward_cached"};
+    "ssim_l1_forward", "ssim_l1_backward", "masked_l1", "depth_to_normal", "blend_forward_cached",
+    "blend_backward_geometry", "blend_backward_color_cached"};
 cudaEvent_t prof_event() {
     if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
     cudaEvent_t e; cudaEventCreate(&e); return e;
@@ -50,6 +51,9 @@ int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4*
                             const float* bg, const float* features, const float* final_T,
                             const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
                             float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream);
+int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
+                                         const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
+                                         float* dL_dfeatures, cudaStream_t stream);
 int sort_num_passes(int end_bit);
 
 static inline int pre_blocks(int P) { return (P + PRE_THREADS - 1) / PRE_THREADS; }
@@ -284,12 +288,29 @@ int r3dgw_blend_forward(int P, int R, int C, const r3dgw_camera* cam, const char
                                       out_color, nullptr, 0, stream_);
 }
 
+int r3dgw_blend_backward_color_cached(int P, int R, int C, const r3dgw_camera* cam, const char* binning_buffer,
+                                      const char* image_buffer, const float* alpha_cache, const float* dL_dpixels,
+                                      float* dL_dfeatures, void* stream_) {
+    if (!cam || !binning_buffer || !image_buffer || !dL_dpixels || !dL_dfeatures || R < 0 || P < 0) return R3DGW_ERR_BAD_ARG;
+    if (R == 0) return 0;
+    if (!alpha_cache) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int W = cam->width, H = cam->height;
+    r3dgw_binning_layout BL; binning_layout(R, W, H, &BL);
+    r3dgw_image_layout IL; image_layout(W, H, &IL);
+    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
+    const float4* A = (const float4*)(binning_buffer + BL.splats);
+    return blend_backward_color_cached_dispatch(C, grid, (const uint2*)(binning_buffer + BL.ranges), A + R, W, H,
+                                                (const uint32_t*)(image_buffer + IL.n_contrib), alpha_cache,
+                                                dL_dpixels, dL_dfeatures, stream);
+}
+
 int r3dgw_blend_backward(int P, int R, int C, const r3dgw_camera* cam, const char* geom_buffer,
                          const char* binning_buffer, const char* image_buffer, const float* features,
                          const float* background, const float* dL_dpixels, float* dL_dmean2D,
                          float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, void* stream_) {
     if (!cam || !binning_buffer || !image_buffer || !background || !dL_dpixels || !dL_dmean2D || !dL_dconic ||
-        !dL_dopacity || !dL_dfeatures || R < 0 || P < 0)
+        !dL_dopacity || R < 0 || P < 0)   // dL_dfeatures == NULL: geometry-only pass
         return R3DGW_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
     const int W = cam->width, H = cam->height;

@@ -360,9 +360,11 @@ constexpr int BWD_WARPS = TILE_PIX / 32;
 #endif
 constexpr bool BWD_DIRECT = R3DGW_BWD_DIRECT_RED != 0;
 
-template <int C, int BATCH>
+// COLOR = false: the geometry-only pass of the deferred drop-in backward (dL/dfeatures already produced per call by
+// blend_backward_color_cached_kernel): 6 reduced values per (warp, splat) instead of 6 + C
+template <int C, int BATCH, bool COLOR = true>
 struct BwdSmem {
-    static constexpr int NV = 6 + C;
+    static constexpr int NV = 6 + (COLOR ? C : 0);
     float4 A[2][BATCH];
     float4 B[2][BATCH];
     float4 feat[2][BATCH * ChanPad<C>::CP / 4];
@@ -372,16 +374,16 @@ struct BwdSmem {
     uint64_t bar[2];
 };
 
-template <int C, int BATCH>
+template <int C, int BATCH, bool COLOR>
 __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatA, const float4* __restrict__ splatB,
     int W, int H, const float* __restrict__ bg_color, const float* __restrict__ features,
     const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpixels, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D,
     float* __restrict__ dL_dopacity, float* __restrict__ dL_dfeatures) {
-    constexpr int NV = 6 + C;
+    constexpr int NV = 6 + (COLOR ? C : 0);
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    BwdSmem<C, BATCH>& s = *reinterpret_cast<BwdSmem<C, BATCH>*>(smem_raw);
+    BwdSmem<C, BATCH, COLOR>& s = *reinterpret_cast<BwdSmem<C, BATCH, COLOR>*>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned lx, ly;
     tile_pixel(tid, lx, ly);
@@ -522,9 +524,11 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                                     accum_rec[p2] = ar;
                                     last_color[p2] = c2;
                                     dLa2 = __ffma2_rn(__ffma2_rn(ar, neg1, c2), dL_dpixel[p2], dLa2);
-                                    const float2 gc = __fmul2_rn(dcd2, dL_dpixel[p2]);
-                                    if (2 * p2 < C) g[6 + 2 * p2] = gc.x;
-                                    if (2 * p2 + 1 < C) g[6 + 2 * p2 + 1] = gc.y;
+                                    if constexpr (COLOR) {
+                                        const float2 gc = __fmul2_rn(dcd2, dL_dpixel[p2]);
+                                        if (2 * p2 < C) g[6 + 2 * p2] = gc.x;
+                                        if (2 * p2 + 1 < C) g[6 + 2 * p2 + 1] = gc.y;
+                                    }
                                 }
                             }
                             float dL_dalpha = dLa2.x + dLa2.y;
@@ -595,6 +599,172 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     }
 }
 
+// -------------------------------------------------------------------------------------------------
+// Colour-only backward over cached alphas (deferred drop-in backward).  render() blends six feature sets over one
+// geometry and autograd runs their backwards one by one; the colour gradient of call i only needs
+//     dL/dfeature[id][c] = sum over pixels of  alpha * T_before * dL/dpixel[c]
+// which is the forward recurrence again, so it is replayed FRONT TO BACK from the alpha cache (no conic, no exp, no
+// T division), reduced over the warp, parked in warp-private shared slots and flushed as one atomic per
+// (tile, splat, channel).  The geometry gradients of all calls are then produced ONCE by blend_backward_kernel
+// <sum C, BATCH, COLOR=false> over the concatenated features / pixel gradients (api: r3dgw_blend_backward with
+// dL_dfeatures == NULL), instead of once per call.
+// -------------------------------------------------------------------------------------------------
+constexpr int BWDC_BATCH = 128;
+template <int C>
+struct BwdColorSmem {
+    float4 B[2][BWDC_BATCH];
+    float acc[TILE_PIX / 32][BWDC_BATCH * C];
+    uint32_t mask[TILE_PIX / 32][BWDC_BATCH / 32];
+    uint16_t list[TILE_PIX / 32][BWDC_BATCH];
+    uint32_t red[TILE_PIX / 32];
+    uint64_t bar[2];
+};
+
+template <int C>
+__global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
+    const uint2* __restrict__ ranges, const float4* __restrict__ splatB, int W, int H,
+    const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
+    const float* __restrict__ dL_dpixels, float* __restrict__ dL_dfeatures) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BwdColorSmem<C>& s = *reinterpret_cast<BwdColorSmem<C>*>(smem_raw);
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned lx, ly;
+    tile_pixel(tid, lx, ly);
+    const uint2 pix = {blockIdx.x * TILE_X + lx, blockIdx.y * TILE_Y + ly};
+    const uint32_t pix_id = W * pix.y + pix.x;
+    const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const uint32_t my_last = inside ? n_contrib[pix_id] : 0u;
+    const uint32_t warp_last = __reduce_max_sync(0xffffffffu, my_last);
+    if (lane == 0) s.red[warp] = warp_last;
+    if (tid == 0) {
+        mbar_init(&s.bar[0], 1);
+        mbar_init(&s.bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    uint32_t tile_last = 0;
+#pragma unroll
+    for (int w = 0; w < TILE_PIX / 32; ++w) tile_last = max(tile_last, s.red[w]);
+    const int total = (int)min(range.y - range.x, tile_last);
+    const int rounds = (total + BWDC_BATCH - 1) / BWDC_BATCH;
+    if (rounds == 0) return;
+    if (tid == 0) {
+        const uint32_t cnt = (uint32_t)min(BWDC_BATCH, total);
+        mbar_expect_tx(&s.bar[0], cnt * 16u);
+        bulk_g2s(s.B[0], splatB + range.x, cnt * 16u, &s.bar[0]);
+    }
+    float dpix[C];
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) dpix[ch] = inside ? dL_dpixels[(size_t)ch * H * W + pix_id] : 0.f;
+    float T = 1.0f;
+    const float* my_rows = alpha_cache + (size_t)range.x * TILE_PIX + tid;
+
+    for (int i = 0; i < rounds; ++i) {
+        const int buf = i & 1;
+        const int cnt = min(BWDC_BATCH, total - i * BWDC_BATCH);
+        mbar_wait(&s.bar[buf], (uint32_t)(i >> 1) & 1u);
+        __syncthreads();   // previous round's flush finished: acc / mask / the other B buffer are free
+        if (lane < BWDC_BATCH / 32) s.mask[warp][lane] = 0;
+        if (tid == 0 && i + 1 < rounds) {
+            const int nb = buf ^ 1;
+            const uint32_t ncnt = (uint32_t)min(BWDC_BATCH, total - (i + 1) * BWDC_BATCH);
+            mbar_expect_tx(&s.bar[nb], ncnt * 16u);
+            bulk_g2s(s.B[nb], splatB + (size_t)range.x + (size_t)(i + 1) * BWDC_BATCH, ncnt * 16u, &s.bar[nb]);
+        }
+        const uint32_t base = (uint32_t)i * BWDC_BATCH;
+        if (base < warp_last) {
+            uint16_t* list = s.list[warp];
+            int nsurv = 0;
+            for (int c0 = 0; c0 < cnt; c0 += 32) {
+                const int jl = c0 + (int)lane;
+                bool keep = false;
+                if (jl < cnt && base + (uint32_t)jl < warp_last) keep = splat_touches_warp(s.B[buf][jl], warp);
+                const unsigned m = __ballot_sync(0xffffffffu, keep);
+                if (keep) list[nsurv + __popc(m & ((1u << lane) - 1u))] = (uint16_t)jl;
+                nsurv += __popc(m);
+            }
+            __syncwarp();
+            const float* rows = my_rows + (size_t)base * TILE_PIX;
+            uint32_t my_mask[BWDC_BATCH / 32];
+#pragma unroll
+            for (int q = 0; q < BWDC_BATCH / 32; ++q) my_mask[q] = 0;
+            for (int g0 = 0; g0 < nsurv; g0 += CACHED_DEPTH) {
+                int js[CACHED_DEPTH];
+                float al[CACHED_DEPTH];
+#pragma unroll
+                for (int u = 0; u < CACHED_DEPTH; ++u) {
+                    js[u] = (g0 + u < nsurv) ? (int)list[g0 + u] : -1;
+                    al[u] = (js[u] >= 0) ? __ldcs(rows + (size_t)js[u] * TILE_PIX) : 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < CACHED_DEPTH; ++u) {
+                    const float alpha = al[u];
+                    if (!__any_sync(0xffffffffu, alpha > 0.f)) continue;
+                    const float w = alpha * T;     // 0 for pixels that did not take the splat
+                    T = T * (1 - alpha);
+                    float g[C];
+#pragma unroll
+                    for (int ch = 0; ch < C; ++ch) g[ch] = w * dpix[ch];
+                    float* slot = &s.acc[warp][js[u] * C];
+                    warp_reduce_multi<C>(g, lane, [&](int vi, float v) { slot[vi] = v; });
+#pragma unroll
+                    for (int q = 0; q < BWDC_BATCH / 32; ++q)
+                        if ((js[u] >> 5) == q) my_mask[q] |= 1u << (js[u] & 31);
+                }
+            }
+            if (lane == 0) {
+#pragma unroll
+                for (int q = 0; q < BWDC_BATCH / 32; ++q) s.mask[warp][q] = my_mask[q];
+            }
+        }
+        __syncthreads();   // all warps' partial sums parked
+        for (int e = (int)tid; e < cnt * C; e += TILE_PIX) {
+            const int jj = e / C;
+            float sum = 0.f;
+            bool any = false;
+#pragma unroll
+            for (int w = 0; w < TILE_PIX / 32; ++w) {
+                if ((s.mask[w][jj >> 5] >> (jj & 31)) & 1u) {
+                    sum += s.acc[w][e];
+                    any = true;
+                }
+            }
+            if (any) {
+                const uint32_t id = __float_as_uint(s.B[buf][jj].w);
+                atomicAdd(dL_dfeatures + (size_t)id * C + (e - jj * C), sum);
+            }
+        }
+    }
+}
+
+template <int C>
+static int launch_backward_color_cached(dim3 grid, const uint2* ranges, const float4* B, int W, int H,
+                                        const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
+                                        float* dL_dfeatures, cudaStream_t stream) {
+    const int smem = (int)sizeof(BwdColorSmem<C>);
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute(blend_backward_color_cached_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    {
+        ProfScope ps(KID_BLEND_BWD_COLOR, stream);
+        blend_backward_color_cached_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, B, W, H, n_contrib, alpha_cache, dL_dpix,
+                                                                              dL_dfeatures);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
+                                         const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
+                                         float* dL_dfeatures, cudaStream_t stream) {
+    switch (C) {
+        case 1: return launch_backward_color_cached<1>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+        case 2: return launch_backward_color_cached<2>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+        case 3: return launch_backward_color_cached<3>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+        case 4: return launch_backward_color_cached<4>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+        default: return R3DGW_ERR_UNSUPPORTED;
+    }
+}
+
 // =================================================================================================
 // host-side dispatch
 // =================================================================================================
@@ -629,17 +799,17 @@ static int launch_forward(dim3 grid, const uint2* ranges, const float4* A, const
     return 0;
 }
 
-template <int C, int BATCH>
+template <int C, int BATCH, bool COLOR>
 static int launch_backward(dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
                            const float* bg, const float* features, const float* final_T,
                            const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
                            float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream) {
-    const int smem = (int)sizeof(BwdSmem<C, BATCH>);
-    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_kernel<C, BATCH>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int smem = (int)sizeof(BwdSmem<C, BATCH, COLOR>);
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_kernel<C, BATCH, COLOR>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     {
-        ProfScope ps(KID_BLEND_BWD, stream);
-        blend_backward_kernel<C, BATCH><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
-                                                                        dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures);
+        ProfScope ps(COLOR ? KID_BLEND_BWD : KID_BLEND_BWD_GEOM, stream);
+        blend_backward_kernel<C, BATCH, COLOR><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
+                                                                               dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;
@@ -662,8 +832,11 @@ int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4*
                             const float* bg, const float* features, const float* final_T,
                             const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
                             float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream) {
+    const bool color = dL_dfeatures != nullptr;   // NULL: geometry-only pass (6 reduced values per splat)
     switch (C) {
-#define R3DGW_BWD_CASE(N, BT) case N: return launch_backward<N, BT>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures, stream);
+#define R3DGW_BWD_CASE(N, BT) case N: return color \
+        ? launch_backward<N, BT, true>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures, stream) \
+        : launch_backward<N, BT, false>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, nullptr, stream);
 #define BT_(direct, parked) (BWD_DIRECT ? direct : parked)
         R3DGW_BWD_CASE(1, BT_(256, 128)) R3DGW_BWD_CASE(2, BT_(256, 128)) R3DGW_BWD_CASE(3, BT_(256, 128))
         R3DGW_BWD_CASE(4, BT_(256, 128)) R3DGW_BWD_CASE(6, BT_(256, 128)) R3DGW_BWD_CASE(8, BT_(128, 64))

@@ -28,7 +28,8 @@ import torch.nn as nn
 from r3dgw_b200 import native as _nat
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
-           "rasterize_gaussians_features", "clear_geometry_cache", "last_geometry_state", "set_alpha_cache"]
+           "rasterize_gaussians_features", "clear_geometry_cache", "last_geometry_state", "set_alpha_cache",
+           "set_deferred_backward"]
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -105,6 +106,8 @@ class GeometryState:
         self.keep = None          # tensors whose storage the camera struct points to
         self.handles = None       # autograd handles (h_mean2D, h_conic, h_opacity, h_rgb)
         # alpha cache (see _BlendFn): filled by the SECOND blend over this geometry, replayed by every later one
+        self.means2D_ref = None
+        self.pending = []         # (features, background, dL_dpixels) of blends whose geometry gradients are deferred
         self.blend_calls = 0
         self.alpha_img = None     # image buffer (final_T, n_contrib) of the pass that filled the cache
 
@@ -197,10 +200,15 @@ class _GeometryFn(torch.autograd.Function):
     """K1..K3 forward; K6+K7 backward.  Outputs are zero-storage handles that only carry gradients."""
 
     @staticmethod
-    def forward(ctx, means3D, opacities, scales, rotations, cov3D_precomp, sh, settings, box):
+    def forward(ctx, means3D, opacities, scales, rotations, cov3D_precomp, sh, settings, box, means2D):
         st = _run_geometry(means3D, opacities, scales, rotations, cov3D_precomp, sh, settings)
         box.append(st)
         ctx.st = st
+        ctx.set_materialize_grads(False)
+        # screen-space means of the call that built this geometry: blends that pass the SAME tensor (render() passes
+        # one screenspace_points to all six calls) can leave its gradient to this node (deferred backward)
+        st.means2D_ref = means2D
+        ctx.means2D_shape = means2D.shape
         ctx.shapes = (means3D.shape, opacities.shape, scales.shape, rotations.shape, cov3D_precomp.shape, sh.shape)
         P, dev = st.P, means3D.device
         z = torch.zeros(1, device=dev)
@@ -214,6 +222,23 @@ class _GeometryFn(torch.autograd.Function):
         m3, op, sc, ro, cv, shc = st.inputs
         P, dev = st.P, m3.device
         L = _nat.lib()
+        g_means2D_in = None
+        if st.pending:
+            # deferred drop-in backward: ONE geometry-only K5 over the concatenated features / pixel gradients of every
+            # blend call that ran its colour-only backward (instead of one full K5 per call)
+            d_mean2D, d_conic, d_opac = _deferred_geometry_pass(st, dev)
+            g_means2D_in = d_mean2D
+            g_mean2D = d_mean2D if g_mean2D is None else d_mean2D + g_mean2D
+            g_conic = d_conic if g_conic is None else d_conic + g_conic
+            g_opacity = d_opac if g_opacity is None else d_opac + g_opacity
+        if g_mean2D is None:
+            g_mean2D = torch.zeros(P, 3, dtype=torch.float32, device=dev)
+        if g_conic is None:
+            g_conic = torch.zeros(P, 4, dtype=torch.float32, device=dev)
+        if g_opacity is None:
+            g_opacity = torch.zeros(P, 1, dtype=torch.float32, device=dev)
+        if g_rgb is None and shc is not None:
+            g_rgb = torch.zeros(P, 3, dtype=torch.float32, device=dev)
         g_mean2D = g_mean2D.contiguous()
         g_conic = g_conic.contiguous()
         flat = torch.zeros(P * (3 + 6 + 3 + 4), dtype=torch.float32, device=dev)
@@ -235,7 +260,11 @@ class _GeometryFn(torch.autograd.Function):
         g_ro = drot if ro is not None else e(3)
         g_cv = dcov3D if cv is not None else e(4)
         g_sh = dsh if shc is not None else e(5)
-        return dmean3D, g_opacity.reshape(ctx.shapes[1]), g_sc, g_ro, g_cv, g_sh, None, None
+        if g_means2D_in is not None and ctx.needs_input_grad[8]:
+            g_means2D_in = g_means2D_in.reshape(ctx.means2D_shape)
+        else:
+            g_means2D_in = None
+        return dmean3D, g_opacity.reshape(ctx.shapes[1]), g_sc, g_ro, g_cv, g_sh, None, None, g_means2D_in
 
 
 class _BlendFn(torch.autograd.Function):
@@ -276,6 +305,7 @@ class _BlendFn(torch.autograd.Function):
             _alpha_pool["owner"], st.alpha_img = st, img
         ctx.st, ctx.C, ctx.use_sh = st, C, use_sh
         ctx.means2D_shape = means2D.shape
+        ctx.means2D_is_ref = means2D is st.means2D_ref
         ctx.feat_shape = features.shape
         ctx.save_for_backward(feats if feats is not None else torch.empty(0, device=dev), bgc, img)
         return out
@@ -290,6 +320,23 @@ class _BlendFn(torch.autograd.Function):
         g = grad_out.contiguous()
         if g.dtype != torch.float32:
             g = g.float()
+        # Deferred drop-in backward: when this geometry's alphas are cached, produce only dL/dfeatures here (front-to-
+        # back replay of the cache) and leave the geometry gradients of ALL blend calls of the frame to one
+        # geometry-only pass in _GeometryFn.backward, which autograd runs after every blend node.
+        cache = st.alpha_cache
+        geo_needed = ctx.needs_input_grad[0] or ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        m2_ok = ctx.means2D_is_ref or not ctx.needs_input_grad[4]
+        if (_DEFER_BWD and cache is not None and not ctx.use_sh and C <= 4 and st.R > 0
+                and ((geo_needed and m2_ok) or (not geo_needed and not ctx.needs_input_grad[4]))):
+            dfeat = torch.zeros(P, C, dtype=torch.float32, device=dev)
+            with torch.cuda.device(dev):
+                rc = L.r3dgw_blend_backward_color_cached(P, st.R, C, ctypes.byref(st.cam), st.binning.data_ptr(),
+                                                         img.data_ptr(), cache.data_ptr(), g.data_ptr(),
+                                                         dfeat.data_ptr(), _stream())
+            _nat.check(rc, "r3dgw_blend_backward_color_cached")
+            if geo_needed:
+                st.pending.append((feats, bgc, g, img))
+            return None, None, None, None, None, dfeat, None, None
         flat = torch.zeros(P * (3 + 4 + 1 + C), dtype=torch.float32, device=dev)
         dmean2D = flat[:3 * P].view(P, 3)
         dconic = flat[3 * P:7 * P].view(P, 4)
@@ -340,6 +387,51 @@ def _alpha_pool_get(nbytes, device):
     return _alpha_pool["buf"]
 
 
+_DEFER_BWD = os.environ.get("R3DGW_DEFERRED_BACKWARD", "1") != "0"
+_BWD_CHANNELS = (32, 27, 24, 18, 16, 15, 12, 9, 8, 6, 4, 3, 2, 1)      # channel counts K5 is instantiated for
+
+
+def set_deferred_backward(enabled: bool):
+    global _DEFER_BWD
+    _DEFER_BWD = bool(enabled)
+
+
+def _deferred_geometry_pass(st, dev):
+    """One geometry-only K5 (r3dgw_blend_backward with dL_dfeatures == NULL) over the concatenation of every pending
+    blend call's features / background / pixel gradients; calls are grouped so that each group's channel total is
+    one the kernel is instantiated for.  Returns (dL_dmean2D[P,3], dL_dconic[P,4], dL_dopacity[P,1])."""
+    pending, st.pending = st.pending, []
+    P = st.P
+    L = _nat.lib()
+    flat = torch.zeros(P * 8, dtype=torch.float32, device=dev)
+    d_mean2D, d_conic, d_opac = flat[:3 * P].view(P, 3), flat[3 * P:7 * P].view(P, 4), flat[7 * P:].view(P, 1)
+    i = 0
+    while i < len(pending):
+        # longest run of calls whose channel total is instantiated
+        best, tot, j = None, 0, i
+        while j < len(pending) and tot + pending[j][0].size(1) <= 32:
+            tot += pending[j][0].size(1)
+            j += 1
+            if tot in _BWD_CHANNELS:
+                best = (j, tot)
+        j, tot = best
+        grp = pending[i:j]
+        if len(grp) == 1:
+            feats, bgc, g = grp[0][0], grp[0][1], grp[0][2]
+        else:
+            feats = torch.cat([e[0] for e in grp], dim=1)
+            bgc = torch.cat([e[1].reshape(-1) for e in grp])
+            g = torch.cat([e[2] for e in grp], dim=0)
+        img = grp[0][3]
+        with torch.cuda.device(dev):
+            rc = L.r3dgw_blend_backward(P, st.R, tot, ctypes.byref(st.cam), st.geom.data_ptr(), st.binning.data_ptr(),
+                                        img.data_ptr(), feats.data_ptr(), bgc.data_ptr(), g.data_ptr(),
+                                        d_mean2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr(), None, _stream())
+        _nat.check(rc, "r3dgw_blend_backward (geometry-only)")
+        i = j
+    return d_mean2D, d_conic, d_opac
+
+
 def set_alpha_cache(enabled: bool):
     global _ALPHA_CACHE
     _ALPHA_CACHE = bool(enabled)
@@ -373,7 +465,7 @@ def _tkey(t):
     return (t.data_ptr(), t._version, tuple(t.shape), tuple(t.stride()), t.requires_grad)
 
 
-def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s):
+def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, means2D):
     grad_mode = torch.is_grad_enabled()
     key = (_tkey(means3D), _tkey(opacities), _tkey(scales), _tkey(rotations), _tkey(cov3Ds_precomp), _tkey(sh),
            int(s.image_height), int(s.image_width), float(s.tanfovx), float(s.tanfovy), float(s.scale_modifier),
@@ -382,7 +474,7 @@ def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s):
     if _CACHE_ENABLED and _cache["key"] == key:
         return _cache["entry"]
     box = []
-    handles = _GeometryFn.apply(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, box)
+    handles = _GeometryFn.apply(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, box, means2D)
     st = box[0]
     # the entry keeps the key tensors alive, so (data_ptr, _version) cannot alias new contents
     entry = (st, handles, (means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s.viewmatrix, s.projmatrix, s.campos))
@@ -399,7 +491,7 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales,
         s = raster_settings
         return (torch.zeros(3, int(s.image_height), int(s.image_width), dtype=torch.float32, device=means3D.device),
                 torch.zeros(0, dtype=torch.int32, device=means3D.device))
-    st, handles, _ = _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, raster_settings)
+    st, handles, _ = _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, raster_settings, means2D)
     h_mean2D, h_conic, h_opacity, h_rgb, radii = handles
     color = _BlendFn.apply(h_mean2D, h_conic, h_opacity, h_rgb, means2D, colors_precomp, raster_settings.bg, st)
     return color, radii
@@ -412,7 +504,8 @@ def rasterize_gaussians_features(means3D, means2D, features, opacities, scales, 
     empty = torch.empty(0, device=means3D.device)
     st, handles, _ = _geometry(means3D, opacities, scales if scales is not None else empty,
                                rotations if rotations is not None else empty,
-                               cov3Ds_precomp if cov3Ds_precomp is not None else empty, empty, raster_settings)
+                               cov3Ds_precomp if cov3Ds_precomp is not None else empty, empty, raster_settings,
+                               means2D)
     h_mean2D, h_conic, h_opacity, h_rgb, radii = handles
     if bg is None:
         bg = torch.zeros(features.size(1), device=means3D.device)
