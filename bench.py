@@ -299,6 +299,9 @@ def l2_flush(torch, buf):
     buf.zero_()          # 512 MiB write > 126 MB L2, outside every timed event pair
 
 
+LAST_STEP_MS = []      # per-step device times of the most recent timed_steps() call (diagnostics on stderr)
+
+
 def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None):
     """W untimed steps, then EXACTLY K steps each bracketed by CUDA events on the current stream (L2 flushed
     between event pairs); barrier + synchronize on both sides; returns total ms (MAX over ranks)."""
@@ -318,7 +321,9 @@ def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None):
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
-    total = sum(a.elapsed_time(b) for a, b in evs)
+    per_step = [a.elapsed_time(b) for a, b in evs]
+    LAST_STEP_MS[:] = per_step
+    total = sum(per_step)
     if dist is not None:
         t = torch.tensor([total], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -547,7 +552,8 @@ def main():
             st.forward(None, st.sky2)
     nf = max(5, args.steps // 2)
     scale_n = world if args.impl == "native" else 1
-    line["fps_fwd"] = scale_n * 1e3 / (timed_steps(torch, frame, nf, 2, flush, dist) / nf)
+    line["fps_fwd"] = scale_n * 1e3 / (timed_steps(torch, frame, nf, 4, flush, dist) / nf)
+    print("fps_fwd per-frame ms:", [round(x, 2) for x in LAST_STEP_MS], file=sys.stderr)
     # relit-eval grid cell (config 4): same view, new environment SH each frame -> geometry (K1..K3) is reused
     line["fps_fwd_relit_same_view"] = scale_n * 1e3 / (timed_steps(torch, lambda: frame(False), nf, 2, flush, dist) / nf)
     s = st.raster.GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, st.bg, 1.0, cam.world_view_transform,
@@ -566,8 +572,9 @@ def main():
         if bwd:
             img.backward(dL)
     n1 = max(5, args.steps // 2)
-    line["u1_raster_call"] = {"fwd_ms": timed_steps(torch, lambda: u1(False), n1, 2, flush, None) / n1,
-                              "fwd_bwd_ms": timed_steps(torch, lambda: u1(True), n1, 2, flush, None) / n1}
+    line["u1_raster_call"] = {"fwd_ms": timed_steps(torch, lambda: u1(False), n1, 4, flush, None) / n1}
+    print("u1 fwd per-call ms:", [round(x, 2) for x in LAST_STEP_MS], file=sys.stderr)
+    line["u1_raster_call"]["fwd_bwd_ms"] = timed_steps(torch, lambda: u1(True), n1, 4, flush, None) / n1
 
     # ---- the single-pass alternative API (render_fused: one 16-channel K4/K5), same step otherwise ------------
     if args.impl == "native" and args.mode == "dropin":

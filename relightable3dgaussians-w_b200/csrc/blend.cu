@@ -422,12 +422,15 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     }
 
     constexpr int CP = ChanPad<C>::CP;
-    float2 accum_rec[CP / 2], last_color[CP / 2], dL_dpixel[CP / 2];   // channel pairs (packed FP32 math below)
+    // The reference carries accum_rec[ch] / last_color[ch] per channel (backward.cu:492-503); both only ever enter
+    // dL/dalpha through their dot product with this pixel's dL/dpixel, and the accum_rec recurrence is linear, so the
+    // whole channel dimension collapses into two scalars: s = <colour_k, dL/dpixel> and A = <accum_rec, dL/dpixel>,
+    // A <- last_alpha * s_last + (1 - last_alpha) * A.  2C fewer live registers and C-independent recurrence cost.
+    float2 dL_dpixel[CP / 2];   // channel pairs (packed FP32 math below)
+    float rec_A = 0.f, rec_s_last = 0.f;
     float bg_dot_dpixel = 0;
 #pragma unroll
     for (int q = 0; q < CP / 2; ++q) {
-        accum_rec[q] = make_float2(0.f, 0.f);
-        last_color[q] = make_float2(0.f, 0.f);
         const int c0 = 2 * q, c1 = 2 * q + 1;
         dL_dpixel[q].x = (inside && c0 < C) ? dL_dpixels[(size_t)c0 * H * W + pix_id] : 0.f;
         dL_dpixel[q].y = (inside && c1 < C) ? dL_dpixels[(size_t)c1 * H * W + pix_id] : 0.f;
@@ -508,11 +511,8 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                             T = T * inv_1ma;
                             const float dchannel_dcolor = alpha * T;
                             // per-channel recurrences on packed FP32 pairs (FFMA2 / FMUL2)
-                            const float2 la2 = make_float2(last_alpha, last_alpha);
-                            const float2 oml2 = make_float2(1.f - last_alpha, 1.f - last_alpha);
                             const float2 dcd2 = make_float2(dchannel_dcolor, dchannel_dcolor);
-                            const float2 neg1 = make_float2(-1.f, -1.f);
-                            float2 dLa2 = make_float2(0.f, 0.f);
+                            float2 dot2 = make_float2(0.f, 0.f);
 #pragma unroll
                             for (int q = 0; q < CP / 4; ++q) {
                                 const float4 f = s.feat[buf][jj * (CP / 4) + q];
@@ -520,10 +520,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                                 for (int h = 0; h < 2; ++h) {
                                     const int p2 = 2 * q + h;
                                     const float2 c2 = h ? make_float2(f.z, f.w) : make_float2(f.x, f.y);
-                                    const float2 ar = __ffma2_rn(la2, last_color[p2], __fmul2_rn(oml2, accum_rec[p2]));
-                                    accum_rec[p2] = ar;
-                                    last_color[p2] = c2;
-                                    dLa2 = __ffma2_rn(__ffma2_rn(ar, neg1, c2), dL_dpixel[p2], dLa2);
+                                    dot2 = __ffma2_rn(c2, dL_dpixel[p2], dot2);
                                     if constexpr (COLOR) {
                                         const float2 gc = __fmul2_rn(dcd2, dL_dpixel[p2]);
                                         if (2 * p2 < C) g[6 + 2 * p2] = gc.x;
@@ -531,8 +528,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                                     }
                                 }
                             }
-                            float dL_dalpha = dLa2.x + dLa2.y;
-                            dL_dalpha *= T;
+                            const float sdot = dot2.x + dot2.y;
+                            rec_A = last_alpha * rec_s_last + (1.f - last_alpha) * rec_A;
+                            rec_s_last = sdot;
+                            float dL_dalpha = (sdot - rec_A) * T;
                             last_alpha = alpha;
                             if (bg_nonzero) dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
                             const float dL_dG = b.y * dL_dalpha;
@@ -703,11 +702,12 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
                     if (!__any_sync(0xffffffffu, alpha > 0.f)) continue;
                     const float w = alpha * T;     // 0 for pixels that did not take the splat
                     T = T * (1 - alpha);
-                    float g[C];
+                    constexpr int CR = (C == 3) ? 4 : C;   // 3 values reduce as a padded chunk of 4: 6 shuffles, not 10
+                    float g[CR];
 #pragma unroll
-                    for (int ch = 0; ch < C; ++ch) g[ch] = w * dpix[ch];
+                    for (int ch = 0; ch < CR; ++ch) g[ch] = ch < C ? w * dpix[ch] : 0.f;
                     float* slot = &s.acc[warp][js[u] * C];
-                    warp_reduce_multi<C>(g, lane, [&](int vi, float v) { slot[vi] = v; });
+                    warp_reduce_multi<CR>(g, lane, [&](int vi, float v) { if (vi < C) slot[vi] = v; });
 #pragma unroll
                     for (int q = 0; q < BWDC_BATCH / 32; ++q)
                         if ((js[u] >> 5) == q) my_mask[q] |= 1u << (js[u] & 31);
@@ -836,7 +836,7 @@ int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4*
     switch (C) {
 #define R3DGW_BWD_CASE(N, BT) case N: return color \
         ? launch_backward<N, BT, true>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures, stream) \
-        : launch_backward<N, BT, false>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, nullptr, stream);
+        : launch_backward<N, 128, false>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, nullptr, stream);
 #define BT_(direct, parked) (BWD_DIRECT ? direct : parked)
         R3DGW_BWD_CASE(1, BT_(256, 128)) R3DGW_BWD_CASE(2, BT_(256, 128)) R3DGW_BWD_CASE(3, BT_(256, 128))
         R3DGW_BWD_CASE(4, BT_(256, 128)) R3DGW_BWD_CASE(6, BT_(256, 128)) R3DGW_BWD_CASE(8, BT_(128, 64))
