@@ -305,9 +305,14 @@ LAST_STEP_MS = []      # per-step device times of the most recent timed_steps() 
 def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None):
     """W untimed steps, then EXACTLY K steps each bracketed by CUDA events on the current stream (L2 flushed
     between event pairs); barrier + synchronize on both sides; returns total ms (MAX over ranks)."""
+    import gc
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
+    # a generation-2 pass of Python's cyclic collector over the interpreter's ~10^5 tracked objects is a 60-150 ms
+    # host stall (seen as single-step outliers): collect now, keep the collector off inside the timed region
+    gc.collect()
+    gc.disable()
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
@@ -321,6 +326,7 @@ def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None):
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
+    gc.enable()
     per_step = [a.elapsed_time(b) for a, b in evs]
     LAST_STEP_MS[:] = per_step
     total = sum(per_step)
@@ -474,6 +480,8 @@ def main():
     torch.cuda.synchronize()
     launches0 = L.r3dgw_launch_count() if L else 0
     total_ms = timed_steps(torch, step_resident, args.steps, 0, flush, dist)
+    if rank == 0:
+        print("step ms (resident):", [round(x, 2) for x in LAST_STEP_MS], file=sys.stderr)
     clocks = sampler.stop()
     gpu_launches = (L.r3dgw_launch_count() - launches0) if L else 0
     ms_per_step = total_ms / args.steps
@@ -531,6 +539,7 @@ def main():
             "config": {"workload": f"{args.workload}: {P} Gaussians, {W}x{H}, 1 view/GPU/step, shade + 6 raster fwd + "
                                    f"5 raster bwd + masked L1/SSIM, sky-BRDF, normal (depth_to_normal), scale and sky-depth "
                                    f"regularisers as train.py:74-116 ({args.mode})", "l2": "512 MiB flush between timed steps",
+                       "host": "Python cyclic GC collected before and disabled inside every timed region",
                        "mode": args.mode, "views_per_step": world},
             "clocks": clocks, "gpu_launches": int(gpu_launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),

@@ -608,13 +608,20 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 // <sum C, BATCH, COLOR=false> over the concatenated features / pixel gradients (api: r3dgw_blend_backward with
 // dL_dfeatures == NULL), instead of once per call.
 // -------------------------------------------------------------------------------------------------
-constexpr int BWDC_BATCH = 128;
+constexpr int BWDC_BATCH = 256;
 template <int C>
 struct BwdColorSmem {
     float4 B[2][BWDC_BATCH];
-    float acc[TILE_PIX / 32][BWDC_BATCH * C];
-    uint32_t mask[TILE_PIX / 32][BWDC_BATCH / 32];
     uint16_t list[TILE_PIX / 32][BWDC_BATCH];
+    // per warp: the blend weights alpha*T of up to 32 pending splats x 32 pixels (row padded to 33: both the
+    // row-wise stores and the column-wise reads are bank-conflict free), their list positions, and the warp's
+    // 32 pixel gradients.  The per-splat reduction over pixels is then W[32x32] . D[32xC], done by 32 lanes at once
+    // (~5 issue slots per splat) instead of a shuffle butterfly per splat (~25); each lane then issues the C
+    // global REDs of its splat (on average 1.6 warps of a tile touch a splat, so parking the partial sums per tile
+    // first would save few atomics and cost a second block barrier per round).
+    float W[TILE_PIX / 32][32][33];
+    uint16_t Wj[TILE_PIX / 32][32];
+    float4 D[TILE_PIX / 32][32];
     uint32_t red[TILE_PIX / 32];
     uint64_t bar[2];
 };
@@ -653,9 +660,13 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
         mbar_expect_tx(&s.bar[0], cnt * 16u);
         bulk_g2s(s.B[0], splatB + range.x, cnt * 16u, &s.bar[0]);
     }
-    float dpix[C];
+    {
+        float dp[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int ch = 0; ch < C; ++ch) dpix[ch] = inside ? dL_dpixels[(size_t)ch * H * W + pix_id] : 0.f;
+        for (int ch = 0; ch < C; ++ch) dp[ch] = inside ? dL_dpixels[(size_t)ch * H * W + pix_id] : 0.f;
+        s.D[warp][lane] = make_float4(dp[0], dp[1], dp[2], dp[3]);
+    }
+    __syncwarp();
     float T = 1.0f;
     const float* my_rows = alpha_cache + (size_t)range.x * TILE_PIX + tid;
 
@@ -663,8 +674,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
         const int buf = i & 1;
         const int cnt = min(BWDC_BATCH, total - i * BWDC_BATCH);
         mbar_wait(&s.bar[buf], (uint32_t)(i >> 1) & 1u);
-        __syncthreads();   // previous round's flush finished: acc / mask / the other B buffer are free
-        if (lane < BWDC_BATCH / 32) s.mask[warp][lane] = 0;
+        __syncthreads();   // every warp is done with the other B buffer
         if (tid == 0 && i + 1 < rounds) {
             const int nb = buf ^ 1;
             const uint32_t ncnt = (uint32_t)min(BWDC_BATCH, total - (i + 1) * BWDC_BATCH);
@@ -672,69 +682,64 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
             bulk_g2s(s.B[nb], splatB + (size_t)range.x + (size_t)(i + 1) * BWDC_BATCH, ncnt * 16u, &s.bar[nb]);
         }
         const uint32_t base = (uint32_t)i * BWDC_BATCH;
-        if (base < warp_last) {
-            uint16_t* list = s.list[warp];
-            int nsurv = 0;
-            for (int c0 = 0; c0 < cnt; c0 += 32) {
-                const int jl = c0 + (int)lane;
-                bool keep = false;
-                if (jl < cnt && base + (uint32_t)jl < warp_last) keep = splat_touches_warp(s.B[buf][jl], warp);
-                const unsigned m = __ballot_sync(0xffffffffu, keep);
-                if (keep) list[nsurv + __popc(m & ((1u << lane) - 1u))] = (uint16_t)jl;
-                nsurv += __popc(m);
+        if (base >= warp_last) continue;
+        uint16_t* list = s.list[warp];
+        int nsurv = 0;
+        for (int c0 = 0; c0 < cnt; c0 += 32) {
+            const int jl = c0 + (int)lane;
+            bool keep = false;
+            if (jl < cnt && base + (uint32_t)jl < warp_last) keep = splat_touches_warp(s.B[buf][jl], warp);
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) list[nsurv + __popc(m & ((1u << lane) - 1u))] = (uint16_t)jl;
+            nsurv += __popc(m);
+        }
+        __syncwarp();
+        const float* rows = my_rows + (size_t)base * TILE_PIX;
+        int pos = 0;   // pending rows of W (warp-uniform)
+        // reduce the pending rows over the 32 pixels: lane l owns row l and issues its splat's C atomics
+        auto reduce_rows = [&](int n) {
+            __syncwarp();
+            if ((int)lane < n) {
+                float o[4] = {0.f, 0.f, 0.f, 0.f};
+                const float* wrow = s.W[warp][lane];
+#pragma unroll 8
+                for (int p = 0; p < 32; ++p) {
+                    const float wv = wrow[p];
+                    const float4 d = s.D[warp][p];
+                    o[0] = fmaf(wv, d.x, o[0]);
+                    if (C > 1) o[1] = fmaf(wv, d.y, o[1]);
+                    if (C > 2) o[2] = fmaf(wv, d.z, o[2]);
+                    if (C > 3) o[3] = fmaf(wv, d.w, o[3]);
+                }
+                const uint32_t id = __float_as_uint(s.B[buf][s.Wj[warp][lane]].w);
+                float* dst = dL_dfeatures + (size_t)id * C;
+#pragma unroll
+                for (int ch = 0; ch < C; ++ch) atomicAdd(dst + ch, o[ch]);
             }
             __syncwarp();
-            const float* rows = my_rows + (size_t)base * TILE_PIX;
-            uint32_t my_mask[BWDC_BATCH / 32];
+        };
+        for (int g0 = 0; g0 < nsurv; g0 += CACHED_DEPTH) {
+            int js[CACHED_DEPTH];
+            float al[CACHED_DEPTH];
 #pragma unroll
-            for (int q = 0; q < BWDC_BATCH / 32; ++q) my_mask[q] = 0;
-            for (int g0 = 0; g0 < nsurv; g0 += CACHED_DEPTH) {
-                int js[CACHED_DEPTH];
-                float al[CACHED_DEPTH];
-#pragma unroll
-                for (int u = 0; u < CACHED_DEPTH; ++u) {
-                    js[u] = (g0 + u < nsurv) ? (int)list[g0 + u] : -1;
-                    al[u] = (js[u] >= 0) ? __ldcs(rows + (size_t)js[u] * TILE_PIX) : 0.f;
-                }
-#pragma unroll
-                for (int u = 0; u < CACHED_DEPTH; ++u) {
-                    const float alpha = al[u];
-                    if (!__any_sync(0xffffffffu, alpha > 0.f)) continue;
-                    const float w = alpha * T;     // 0 for pixels that did not take the splat
-                    T = T * (1 - alpha);
-                    constexpr int CR = (C == 3) ? 4 : C;   // 3 values reduce as a padded chunk of 4: 6 shuffles, not 10
-                    float g[CR];
-#pragma unroll
-                    for (int ch = 0; ch < CR; ++ch) g[ch] = ch < C ? w * dpix[ch] : 0.f;
-                    float* slot = &s.acc[warp][js[u] * C];
-                    warp_reduce_multi<CR>(g, lane, [&](int vi, float v) { if (vi < C) slot[vi] = v; });
-#pragma unroll
-                    for (int q = 0; q < BWDC_BATCH / 32; ++q)
-                        if ((js[u] >> 5) == q) my_mask[q] |= 1u << (js[u] & 31);
-                }
+            for (int u = 0; u < CACHED_DEPTH; ++u) {
+                js[u] = (g0 + u < nsurv) ? (int)list[g0 + u] : -1;
+                al[u] = (js[u] >= 0) ? __ldcs(rows + (size_t)js[u] * TILE_PIX) : 0.f;
             }
-            if (lane == 0) {
 #pragma unroll
-                for (int q = 0; q < BWDC_BATCH / 32; ++q) s.mask[warp][q] = my_mask[q];
+            for (int u = 0; u < CACHED_DEPTH; ++u) {
+                const float alpha = al[u];
+                if (!__any_sync(0xffffffffu, alpha > 0.f)) continue;
+                s.W[warp][pos][lane] = alpha * T;     // 0 for pixels that did not take the splat
+                T = T * (1 - alpha);
+                if (lane == 0) s.Wj[warp][pos] = (uint16_t)js[u];
+                if (++pos == 32) {
+                    reduce_rows(32);
+                    pos = 0;
+                }
             }
         }
-        __syncthreads();   // all warps' partial sums parked
-        for (int e = (int)tid; e < cnt * C; e += TILE_PIX) {
-            const int jj = e / C;
-            float sum = 0.f;
-            bool any = false;
-#pragma unroll
-            for (int w = 0; w < TILE_PIX / 32; ++w) {
-                if ((s.mask[w][jj >> 5] >> (jj & 31)) & 1u) {
-                    sum += s.acc[w][e];
-                    any = true;
-                }
-            }
-            if (any) {
-                const uint32_t id = __float_as_uint(s.B[buf][jj].w);
-                atomicAdd(dL_dfeatures + (size_t)id * C + (e - jj * C), sum);
-            }
-        }
+        if (pos > 0) reduce_rows(pos);   // before the next round's barrier lets B[buf] be overwritten
     }
 }
 
