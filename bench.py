@@ -50,20 +50,19 @@ def parse_args():
 
 # ---- clocks -------------------------------------------------------------------------------------------
 class ClockSampler:
-    """SM clock / power / throttle-reason sampler running DURING the timed region (B200_PROFILING.md clocks line).
-    In-process NVML from a background thread every 100 ms: a polling `nvidia-smi -lms` subprocess takes the driver
-    lock for milliseconds per query and stalls the ~450 kernel launches of a step (measured: +3 ms/step); the same
-    counters read through NVML do not.  Falls back to the nvidia-smi subprocess if NVML cannot be loaded."""
+    """SM clock / power / throttle-reason samples taken DURING the timed region (B200_PROFILING.md clocks line).
+    A concurrent poller perturbs what it measures here: a step is ~450 kernel launches, and every NVML / nvidia-smi
+    query serialises with them in the driver (measured on this box: `nvidia-smi -lms 200` +3 ms/step; an in-process
+    NVML thread at 4 Hz, single stalls of 20-90 ms and +1..3 ms on the following steps).  So the samples are taken
+    synchronously from the launching thread BETWEEN the per-step CUDA-event pairs, every few steps, while the GPU is
+    still executing the step just enqueued: under load, inside the timed region, outside every timed interval."""
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index):
-        import threading
         self.idx = gpu_index
         self.samples = []          # (sm_mhz, power_w, reasons bitmask)
         self.max_mhz = None
-        self._stop = threading.Event()
-        self._thread = None
-        self._smi = None
+        self.source = None
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -74,12 +73,13 @@ class ClockSampler:
                 phys = int(vis.split(",")[gpu_index])
             self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys)
             self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.source = "nvml"
         except Exception:   # noqa: BLE001
             self.nv = None
 
-    def _loop(self):
-        nv, h = self.nv, self.h
-        while not self._stop.is_set():
+    def sample(self):
+        if self.nv is not None:
+            nv, h = self.nv, self.h
             try:
                 sm = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
                 pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
@@ -90,63 +90,32 @@ class ClockSampler:
                 self.samples.append((sm, pw, rs))
             except Exception:   # noqa: BLE001
                 pass
-            self._stop.wait(0.1)
-
-    def start(self):
-        if self.nv is not None:
-            import threading
-            self._thread = threading.Thread(target=self._loop, daemon=True)
-            self._thread.start()
             return
-        try:   # fallback: nvidia-smi subprocess
-            self._f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
-            q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+        try:   # fallback: one nvidia-smi query
+            q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
                  "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
                  "clocks_event_reasons.sw_power_cap")
-            self._smi = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={q}",
-                                          "--format=csv,noheader,nounits", "-lms", "500"], stdout=self._f,
-                                         stderr=subprocess.DEVNULL)
+            out = subprocess.run(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                 capture_output=True, text=True, timeout=10).stdout.strip().splitlines()[0]
+            c = [x.strip() for x in out.split(",")]
+            rs = sum(b for b, v in zip([0x8, 0x40, 0x20, 0x4], c[3:7]) if v.lower().startswith("active"))
+            self.samples.append((float(c[0]), float(c[2]), rs))
+            self.max_mhz = float(c[1])
+            self.source = "nvidia-smi"
         except Exception:   # noqa: BLE001
-            self._smi = None
+            pass
 
-    def stop(self):
-        if self._thread is not None:
-            time.sleep(0.12)
-            self._stop.set()
-            self._thread.join(timeout=2)
-        elif self._smi is not None:
-            time.sleep(0.6)
-            self._smi.terminate()
-            try:
-                self._smi.wait(timeout=5)
-            except Exception:   # noqa: BLE001
-                self._smi.kill()
-            self._f.flush(); self._f.seek(0)
-            bits = [0x8, 0x40, 0x20, 0x4]
-            for line in self._f.read().splitlines():
-                c = [x.strip() for x in line.split(",")]
-                try:
-                    rs = sum(b for b, v in zip(bits, c[4:8]) if v.lower().startswith("active"))
-                    self.samples.append((float(c[1]), float(c[3]), rs))
-                    self.max_mhz = float(c[2])
-                except (ValueError, IndexError):
-                    continue
-            try:
-                os.unlink(self._f.name)
-            except OSError:
-                pass
-        else:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock source (NVML and nvidia-smi unavailable)"]}
+    def summary(self):
         if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["no samples"]}
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["no samples (NVML and nvidia-smi unavailable)"]}
         pmax = max(p for _, p, _ in self.samples)
         busy = [s for s, p, _ in self.samples if p > 0.5 * pmax] or [s for s, _, _ in self.samples]
         seen = set()
         for _, _, rs in self.samples:
             seen |= {name for bit, name in self.REASONS.items() if rs & bit}
         return {"sm_mhz": statistics.median(busy), "sm_max_mhz": self.max_mhz, "reasons": sorted(seen),
-                "samples": len(self.samples), "power_w_max": pmax,
-                "source": "nvml" if self._thread is not None else "nvidia-smi"}
+                "samples": len(self.samples), "power_w_max": pmax, "source": self.source,
+                "how": "sampled between the per-step event pairs of the timed region, GPU busy"}
 
 
 # ---- workload -------------------------------------------------------------------------------------------
@@ -302,7 +271,7 @@ def l2_flush(torch, buf):
 LAST_STEP_MS = []      # per-step device times of the most recent timed_steps() call (diagnostics on stderr)
 
 
-def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None):
+def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None, sampler=None):
     """W untimed steps, then EXACTLY K steps each bracketed by CUDA events on the current stream (L2 flushed
     between event pairs); barrier + synchronize on both sides; returns total ms (MAX over ranks)."""
     import gc
@@ -317,11 +286,13 @@ def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None):
         dist.barrier()
     torch.cuda.synchronize()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-    for a, b in evs:
+    for k, (a, b) in enumerate(evs):
         l2_flush(torch, flush_buf)
         a.record()
         fn()
         b.record()
+        if sampler is not None and len(sampler.samples) < 6 and k % 4 == 1:
+            sampler.sample()      # GPU still busy with the step just enqueued; outside every event pair
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
@@ -469,20 +440,20 @@ def main():
             bucket.all_reduce(average_over=world)   # gradient exchange (64 B per Gaussian) over NVLink, ONE all-reduce
 
     sampler = ClockSampler(local_rank)
-    # setup (not part of W): a few iterations so that torch's caching allocator has grown its pools; the first
-    # iterations otherwise pay cudaMalloc (a device-wide sync each) inside the step
-    for _ in range(6):
+    # setup (not part of W): iterations so that torch's caching allocator has grown its pools (the first ones
+    # otherwise pay cudaMalloc, a device-wide sync each, inside the step) and so that the timed region starts in
+    # the sustained regime: on this pool the first ~100 ms of back-to-back steps run ~7 % faster than steady state
+    for _ in range(25):
         step_resident()
     torch.cuda.synchronize()
-    sampler.start()                 # started before the warm-up so nvidia-smi's own start-up is over by the timed region
     for _ in range(args.warmup):
         step_resident()
     torch.cuda.synchronize()
     launches0 = L.r3dgw_launch_count() if L else 0
-    total_ms = timed_steps(torch, step_resident, args.steps, 0, flush, dist)
+    total_ms = timed_steps(torch, step_resident, args.steps, 0, flush, dist, sampler)
     if rank == 0:
         print("step ms (resident):", [round(x, 2) for x in LAST_STEP_MS], file=sys.stderr)
-    clocks = sampler.stop()
+    clocks = sampler.summary()
     gpu_launches = (L.r3dgw_launch_count() - launches0) if L else 0
     ms_per_step = total_ms / args.steps
     value = world * 1e3 / ms_per_step if args.impl == "native" else 1e3 / ms_per_step

@@ -426,6 +426,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     // dL/dalpha through their dot product with this pixel's dL/dpixel, and the accum_rec recurrence is linear, so the
     // whole channel dimension collapses into two scalars: s = <colour_k, dL/dpixel> and A = <accum_rec, dL/dpixel>,
     // A <- last_alpha * s_last + (1 - last_alpha) * A.  2C fewer live registers and C-independent recurrence cost.
+    // (s - A subtracts two rounded dot products: an error of ~1e-7 |s|, three orders of magnitude below the
+    // atomic-order noise of the reference's own gradients, profiles/r01_grad_l2.txt.  The cancellation-free form
+    // E_k = <colour_k - colour_last, dL/dpixel> + (1 - last_alpha) E_last was measured: same errors, 18 % slower.)
     float2 dL_dpixel[CP / 2];   // channel pairs (packed FP32 math below)
     float rec_A = 0.f, rec_s_last = 0.f;
     float bg_dot_dpixel = 0;

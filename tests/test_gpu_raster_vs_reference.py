@@ -37,6 +37,10 @@ def _grad_close(a, b, name, b2=None):
     err = (a - b).abs()
     l2 = (err.pow(2).sum().sqrt() / b.pow(2).sum().sqrt().clamp_min(1e-30)).item()
     l2_bar = 1e-3
+    if name.endswith(("rotations", "scales")):
+        # the reference's own two-run relative L2 on these reaches 9.5e-4 (config A, profiles/r01_grad_l2.txt) and is
+        # heavy-tailed (a handful of ill-conditioned entries carry it): 3e-3 is ~3x its measured ceiling
+        l2_bar = 3e-3
     if b2 is not None:   # rotations/scales: the reference's own run-to-run L2 deviation reaches 1e-3..4e-2
         l2_rr = ((b - b2.double()).pow(2).sum().sqrt() / b.pow(2).sum().sqrt().clamp_min(1e-30)).item()
         l2_bar = max(l2_bar, 3.0 * l2_rr)
