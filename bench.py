@@ -331,6 +331,35 @@ def algorithmic_bytes(kernel, P, Pv, R, N, tiles, C, n_pass):
     return table.get(kernel)
 
 
+def alpha_cache_rows(st, dgr):
+    """Number of 128-byte alpha-cache rows a replay kernel reads for the geometry state `st`: (list entry, warp) pairs
+    whose footprint-cull bit is set and whose list position lies before that warp's deepest contributor.  Counted
+    with torch ops from the state buffers (B stream cull bits, tile ranges, n_contrib) - bench bookkeeping only."""
+    import ctypes
+    import torch
+    from r3dgw_b200 import native
+    L = native.lib()
+    BL, IL = native.BinningLayout(), native.ImageLayout()
+    L.r3dgw_get_binning_layout(st.R, st.W, st.H, ctypes.byref(BL))
+    L.r3dgw_get_image_layout(st.W, st.H, ctypes.byref(IL))
+    R, W, H = st.R, st.W, st.H
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    ranges = st.binning[BL.ranges:BL.ranges + gx * gy * 8].view(torch.int32).view(-1, 2).long()
+    Bz = st.binning[BL.splats + 16 * R:BL.splats + 32 * R].view(torch.int32).view(R, 4)[:, 2]
+    ncon = st.alpha_img[IL.n_contrib:IL.n_contrib + 4 * W * H].view(torch.int32).view(H, W).long()
+    pad = torch.zeros(gy * 16, gx * 16, dtype=torch.long, device=ncon.device)
+    pad[:H, :W] = ncon
+    # warp w of a tile covers columns (w&1)*8.., rows (w>>1)*4..  ->  [tiles, 8] deepest contributor per warp
+    wl = pad.view(gy, 4, 4, gx, 2, 8).amax(dim=(2, 5)).permute(0, 2, 1, 3).reshape(gy * gx, 8)
+    lens = (ranges[:, 1] - ranges[:, 0]).clamp_min(0)
+    tile_of = torch.repeat_interleave(torch.arange(gx * gy, device=ncon.device), lens)
+    local = torch.arange(R, device=ncon.device) - ranges[tile_of, 0]
+    rows = 0
+    for w in range(8):
+        rows += int((((Bz >> w) & 1).bool() & (local < wl[tile_of, w])).sum().item())
+    return rows
+
+
 def cpu_baseline(workload, budget_s=20.0):
     """The CPU port of the reference path (oracle/, OpenMP over all host cores) on a bounded sample of the workload:
     the first P/f Gaussians at full resolution, one raster fwd+bwd (C=3) + torch-CPU shading fwd+bwd, extrapolated to
@@ -594,7 +623,15 @@ def main():
                 for k, (ms, n) in prof.items() if n}
         # kernels that replay the alpha cache have no closed-form byte count (rows surviving the footprint cull are
         # data dependent): they are listed in `kernels` but the roofline object is for the top kernel with one
-        known = [k for k in kern if algorithmic_bytes(k, P, Pv, Rn, N, tiles, 3, n_pass) is not None]
+        gs_now = dgr.last_geometry_state()
+        rows = alpha_cache_rows(gs_now, dgr) if (gs_now is not None and gs_now.alpha_cache is not None) else 0
+        extra = {   # replay kernels: cache rows (128 B each) + B stream + per-pixel inputs / outputs (+ reduced gradient)
+            "blend_forward_cached": 128 * rows + (16 + 4 * 3) * Rn + (4 * 3 + 8) * N,
+            "blend_backward_color_cached": 128 * rows + 16 * Rn + (4 * 3 + 4) * N + 4 * 3 * Pv,
+        }
+        _ab = algorithmic_bytes
+        algorithmic_bytes_x = lambda k, *a: extra[k] if (k in extra and rows) else _ab(k, *a)   # noqa: E731
+        known = [k for k in kern if algorithmic_bytes_x(k, P, Pv, Rn, N, tiles, 3, n_pass) is not None]
         top = max(known, key=lambda k: kern[k]["ms_per_step"])
         if top == "blend_backward_geometry":
             C = 15
@@ -604,11 +641,11 @@ def main():
         except Exception:   # noqa: BLE001
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        ab = algorithmic_bytes(top, P, Pv, Rn, N, tiles, C, n_pass)
+        ab = algorithmic_bytes_x(top, P, Pv, Rn, N, tiles, C, n_pass)
         ach = ab / (kern[top]["avg_launch_ms"] * 1e-3) / 1e9
         traffic = None       # dram__bytes_read+write per launch from the committed `ncu --set full` capture (C = 3, config B)
         try:
-            if args.workload == "B" and C == 3:
+            if args.workload == "B":
                 traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))[top]["dram_traffic_bytes_per_launch"]
         except Exception:   # noqa: BLE001
             pass
@@ -625,7 +662,12 @@ def main():
         line["roofline_fwd_call"] = {"achieved": fwd_gbs, "peak": peak, "frac": fwd_gbs / peak, "unit": "GB/s",
                                      "algorithmic_bytes": fwd_bytes}
         line["kernels"] = {k: {a: round(b, 5) for a, b in v.items()} for k, v in kern.items()}
-        line["scene"] = {"P": P, "P_visible": Pv, "R": Rn, "pixels": N, "tiles": tiles, "sort_passes": n_pass}
+        line["scene"] = {"P": P, "P_visible": Pv, "R": Rn, "pixels": N, "tiles": tiles, "sort_passes": n_pass,
+                         "alpha_cache_rows": rows}
+        # every kernel of the step against the HBM roofline (algorithmic bytes / measured launch time / peak)
+        line["roofline_all"] = {k: round(algorithmic_bytes_x(k, P, Pv, Rn, N, tiles, 15 if k == "blend_backward_geometry" else C, n_pass)
+                                         / (kern[k]["avg_launch_ms"] * 1e-3) / 1e9 / peak, 4) for k in known}
+        # (masked_l1 / ssim rows count each image once; a launch that re-reads L2-resident images can exceed 1)
 
     if args.impl == "native" and rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.workload)
