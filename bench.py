@@ -313,8 +313,11 @@ def algorithmic_bytes(kernel, P, Pv, R, N, tiles, C, n_pass):
     table = {
         "preprocess_scan": 44 * P + 8 * P + 52 * Pv + 8 * P,                   # K1 + fused scan (B_pre + B_scan)
         "duplicate_keys": 20 * P + 12 * R,
-        "sort_histogram": 8 * R,
-        "sort_onesweep_pass": 24 * R,                                          # per pass: read 12 + write 12
+        # depth-first binning: the per-Gaussian depth sort (keys kernel + histogram + 4 passes over P 8-byte pairs) is
+        # work the reference does not have; the R-sized sort moves 32-bit tile ids + ids (16 B per pass)
+        "depth_sort": (8 + 8 + 4 + 4 * 16) * P,
+        "sort_histogram": 4 * R,
+        "sort_onesweep_pass": 16 * R,                                          # per pass: read 8 + write 8
         "ranges_gather": 12 * R + 8 * tiles + 24 * R + 32 * R,                 # keys+ids, gather xy/conic, write stream
         "blend_forward": (32 + 4 * C) * R + (4 * C + 8) * N,
         "blend_backward": (32 + 4 * C) * R + (4 * C + 8) * N + (4 * C + 24) * Pv,
@@ -606,7 +609,7 @@ def main():
         gs = dgr.last_geometry_state()
         Rn, Pv = int(gs.R), int((gs.radii > 0).sum().item())
         N, tiles = W * H, ((W + 15) // 16) * ((H + 15) // 16)
-        n_pass = (32 + int(tiles).bit_length() + 7) // 8
+        n_pass = (int(tiles).bit_length() + 7) // 8      # passes of the R-sized tile-id sort
         C = 16 if args.mode == "fused" else 3
         torch.cuda.synchronize()
         native.profile_read(reset=True)
@@ -655,12 +658,17 @@ def main():
                             "algorithmic_bytes_per_launch": ab, "avg_launch_ms": kern[top]["avg_launch_ms"],
                             "share_of_step_kernel_time": kern[top]["ms_per_step"] / step_kernel_ms}
         # whole forward U1 (K1..K4, C=3) against the HBM roofline - north_star's "render fwd" figure
-        fwd_bytes = sum(algorithmic_bytes(k, P, Pv, Rn, N, tiles, 3, n_pass) * (n_pass if k == "sort_onesweep_pass" else 1)
-                        for k in ("preprocess_scan", "duplicate_keys", "sort_histogram", "sort_onesweep_pass",
-                                  "ranges_gather", "blend_forward"))
-        fwd_gbs = fwd_bytes / (line["u1_raster_call"]["fwd_ms"] * 1e-3) / 1e9
+        # (a) SURVEY 8(d)'s closed form for the reference algorithm (one 6-pass sort of 64-bit keys): comparable
+        #     across rounds and designs;  (b) the bytes THIS pipeline's forward kernels must move (depth-first binning)
+        fwd_bytes = 132 * P + (200 + 4 * 3) * Rn + (4 * 3 + 8) * N + 8 * tiles
+        own_bytes = sum(algorithmic_bytes(k, P, Pv, Rn, N, tiles, 3, n_pass) * (n_pass if k == "sort_onesweep_pass" else 1)
+                        for k in ("preprocess_scan", "depth_sort", "duplicate_keys", "sort_histogram",
+                                  "sort_onesweep_pass", "ranges_gather", "blend_forward"))
+        fwd_s = line["u1_raster_call"]["fwd_ms"] * 1e-3
+        fwd_gbs = fwd_bytes / fwd_s / 1e9
         line["roofline_fwd_call"] = {"achieved": fwd_gbs, "peak": peak, "frac": fwd_gbs / peak, "unit": "GB/s",
-                                     "algorithmic_bytes": fwd_bytes}
+                                     "algorithmic_bytes": fwd_bytes, "bytes_definition": "SURVEY 8d B_fwd(C=3), reference algorithm",
+                                     "own_pipeline_bytes": own_bytes, "own_frac": own_bytes / fwd_s / 1e9 / peak}
         line["kernels"] = {k: {a: round(b, 5) for a, b in v.items()} for k, v in kern.items()}
         line["scene"] = {"P": P, "P_visible": Pv, "R": Rn, "pixels": N, "tiles": tiles, "sort_passes": n_pass,
                          "alpha_cache_rows": rows}

@@ -64,14 +64,17 @@ typedef struct r3dgw_geom_layout {
     size_t rgb;            /* f32[3P]    SH->RGB result (only when shs are given)       */
     size_t clamped;        /* u8[3P]                                                    */
     size_t scan_state;     /* u64[blocks] decoupled look-back tile states               */
+    size_t depth_sort;     /* per-Gaussian depth sort of the depth-first binning: u32 keys[P], keys_alt[P], ids[P],
+                              ids_alt[P], radix workspace, K2' look-back states            */
     size_t total;
 } r3dgw_geom_layout;
 
 typedef struct r3dgw_binning_layout {
     size_t point_list;          /* u32[R]   sorted Gaussian ids                          */
-    size_t point_list_keys;     /* u64[R]   sorted (tile<<32 | depth bits) keys          */
+    size_t point_list_keys;     /* u64[R]   sorted (tile<<32 | depth bits) keys - filled on demand by
+                                             r3dgw_materialize_sorted_keys (the pipeline sorts 32-bit tile ids) */
     size_t point_list_alt;      /* u32[R]   ping-pong value buffer                       */
-    size_t point_list_keys_alt; /* u64[R]   ping-pong key buffer                         */
+    size_t point_list_keys_alt; /* u32[R] x 2 tile-id keys (sorted result in the first half) */
     size_t ranges;              /* uint2[tiles]                                          */
     size_t splats;              /* 2 x float4[R] sorted-order splat stream */
     size_t sort_hist;           /* u32 radix histograms + look-back state                */
@@ -103,8 +106,10 @@ int r3dgw_profile_read(double* total_ms, uint64_t* launches, int reset);
 
 /* ---- staged pipeline ------------------------------------------------------------------------ */
 
-/* K1 preprocess (+fused prefix sum) -> D2H of num_rendered -> K2 duplicate -> onesweep radix sort
- * -> K3 tile ranges + splat-stream gather.   Reference: rasterizer_impl.cu:216-318. */
+/* K1 preprocess (+fused prefix sum) -> per-Gaussian depth sort (P 32-bit keys) -> D2H of num_rendered -> K2'
+ * duplicates in depth order (tile-id keys) -> stable onesweep radix sort on the tile bits only -> K3 tile ranges +
+ * splat-stream gather.  Same sorted order as the reference's single (tile|depth) sort.
+ * Reference: rasterizer_impl.cu:216-318. */
 int r3dgw_geometry_forward(
     r3dgw_alloc_fn geom_alloc, void* geom_ctx,
     r3dgw_alloc_fn binning_alloc, void* binning_ctx,
@@ -115,6 +120,11 @@ int r3dgw_geometry_forward(
     int* radii,            /* out, i32[P] */
     int* num_rendered,     /* out, host   */
     void* stream);
+
+/* Rebuilds the reference's sorted 64-bit keys (tile << 32 | depth bits, rasterizer_impl.cu:70-111, 303-308) in
+ * binning.point_list_keys from the sorted tile ids, the sorted point list and the depths (tests / tooling). */
+int r3dgw_materialize_sorted_keys(int P, int R, int width, int height, const char* geom_buffer,
+                                  char* binning_buffer, void* stream);
 
 /* K4: front-to-back blend of C-channel per-Gaussian features over the cached geometry.
  * features == NULL selects the SH->RGB colours in the geometry buffer (C must be 3).

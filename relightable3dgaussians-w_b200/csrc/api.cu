@@ -15,6 +15,7 @@ std::atomic<uint64_t> g_launches{0};
 
 // ---- per-kernel timing registry ---------------------------------------------------------------------
 bool g_profile_on = false;
+int g_sort_prof_kid = -1;
 namespace {
 struct ProfSpan { int id; cudaEvent_t e0, e1; };
 std::mutex g_prof_mu;
@@ -26,7 +27,7 @@ const char* const g_prof_names[KID_COUNT] = {
     "preprocess_scan", "duplicate_keys", "sort_histogram", "sort_scan", "sort_onesweep_pass", "ranges_gather",
     "blend_forward", "blend_backward", "geometry_backward", "shade_forward", "shade_backward", "knn", "mark_visible",
     "ssim_l1_forward", "ssim_l1_backward", "masked_l1", "depth_to_normal", "blend_forward_cached",
-    "blend_backward_geometry", "blend_backward_color_cached"};
+    "blend_backward_geometry", "blend_backward_color_cached", "depth_sort"};
 cudaEvent_t prof_event() {
     if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
     cudaEvent_t e; cudaEventCreate(&e); return e;
@@ -58,6 +59,22 @@ int sort_num_passes(int end_bit);
 
 static inline int pre_blocks(int P) { return (P + PRE_THREADS - 1) / PRE_THREADS; }
 
+// depth-first binning scratch inside the geometry buffer: keys | keys_alt | ids | ids_alt | radix workspace |
+// K2' look-back states (+ ticket)
+struct DepthSortLayout { size_t keys, keys_alt, ids, ids_alt, ws, dup_state, total; };
+static DepthSortLayout depth_sort_layout(int P) {
+    DepthSortLayout D;
+    const size_t Ps = (size_t)(P > 0 ? P : 0);
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 256); return at; };
+    D.keys = take(Ps * 4); D.keys_alt = take(Ps * 4); D.ids = take(Ps * 4); D.ids_alt = take(Ps * 4);
+    D.ws = take(sort_workspace_bytes(P));
+    D.dup_state = take(((Ps + 255) / 256) * 8 + 16);
+    D.total = o;
+    return D;
+}
+static size_t depth_sort_bytes(int P) { return depth_sort_layout(P).total; }
+
 void geom_layout(int P, int has_sh, r3dgw_geom_layout* L) {
     size_t o = 0;
     const size_t Ps = (size_t)(P > 0 ? P : 0);
@@ -71,6 +88,7 @@ void geom_layout(int P, int has_sh, r3dgw_geom_layout* L) {
     L->rgb = take(has_sh ? Ps * 12 : 0);
     L->clamped = take(has_sh ? Ps * 3 : 0);
     L->scan_state = take((size_t)pre_blocks(P) * 8 + 16);   // +16: device scalar holding R
+    L->depth_sort = take(depth_sort_bytes(P));
     L->total = o;
 }
 
@@ -208,6 +226,28 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
             preprocess_scan_kernel<<<blocks, PRE_THREADS, 0, stream>>>(pp);
         }
         R3DGW_LAUNCH_CHECK();
+        // depth-first binning, step 1: stable sort of the P Gaussians by depth bits - enqueued BEFORE the read-back of
+        // R so that it runs while the host waits
+        {
+            const DepthSortLayout DS = depth_sort_layout(P);
+            char* ds = g + GL.depth_sort;
+            R3DGW_CUDA_TRY(cudaMemsetAsync(ds + DS.dup_state, 0, ((size_t)(P + 255) / 256) * 8 + 16, stream));
+            {
+                {
+                    ProfScope ps(KID_DEPTH_SORT, stream);
+                    depth_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, pp.depths, radii, (uint32_t*)(ds + DS.keys),
+                                                                          (uint32_t*)(ds + DS.ids));
+                }
+                R3DGW_LAUNCH_CHECK();
+                uint32_t* dks; uint32_t* dvs;
+                g_sort_prof_kid = KID_DEPTH_SORT;
+                int rc = sort_pairs_u32_u32((uint32_t*)(ds + DS.keys), (uint32_t*)(ds + DS.keys_alt), (uint32_t*)(ds + DS.ids),
+                                            (uint32_t*)(ds + DS.ids_alt), P, 32, ds + DS.ws, stream, &dks, &dvs);
+                g_sort_prof_kid = -1;
+                if (rc) return rc;
+                if (dvs != (uint32_t*)(ds + DS.ids)) return R3DGW_ERR_BAD_ARG;   // 4 passes: back in the main buffer
+            }
+        }
         // the one blocking read-back of the path (reference: rasterizer_impl.cu:281)
         R3DGW_CUDA_TRY(cudaMemcpyAsync(&R, pp.total_out, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
         R3DGW_CUDA_TRY(cudaStreamSynchronize(stream));
@@ -222,37 +262,54 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
     *num_rendered = (int)R;
     if (R == 0) return 0;
 
-    const int end_bit = 32 + bit_length(gx * gy);
+    // depth-first binning, steps 2-3: duplicates in depth order with tile-id keys, stable sort on the tile bits only
+    const int end_bit = bit_length(gx * gy);
     const int passes = sort_num_passes(end_bit);
-    // choose the starting buffer so that the sorted result lands in point_list / point_list_keys
-    uint64_t* keys_main = (uint64_t*)(b + BL.point_list_keys);
-    uint64_t* keys_alt = (uint64_t*)(b + BL.point_list_keys_alt);
+    uint32_t* tk_main = (uint32_t*)(b + BL.point_list_keys_alt);
+    uint32_t* tk_alt = tk_main + R;
     uint32_t* vals_main = (uint32_t*)(b + BL.point_list);
     uint32_t* vals_alt = (uint32_t*)(b + BL.point_list_alt);
-    uint64_t* k0 = (passes & 1) ? keys_alt : keys_main;
-    uint64_t* k1 = (passes & 1) ? keys_main : keys_alt;
+    // choose the starting buffer so that the sorted result lands in point_list / the first key half
+    uint32_t* k0 = (passes & 1) ? tk_alt : tk_main;
+    uint32_t* k1 = (passes & 1) ? tk_main : tk_alt;
     uint32_t* v0 = (passes & 1) ? vals_alt : vals_main;
     uint32_t* v1 = (passes & 1) ? vals_main : vals_alt;
-
+    const DepthSortLayout DS = depth_sort_layout(P);
+    char* ds = g + GL.depth_sort;
     {
         ProfScope ps(KID_DUPLICATE, stream);
-        duplicate_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
-            P, (const float2*)(g + GL.means2D), (const float*)(g + GL.depths),
-            (const uint32_t*)(g + GL.point_offsets), k0, v0, radii, gx, gy);
+        duplicate_sorted_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
+            P, (const uint32_t*)(ds + DS.ids), (const uint32_t*)(g + GL.tiles_touched), (const float2*)(g + GL.means2D),
+            radii, (unsigned long long*)(ds + DS.dup_state),
+            (uint32_t*)(ds + DS.dup_state + ((size_t)(P + 255) / 256) * 8), k0, v0, gx, gy);
     }
     R3DGW_LAUNCH_CHECK();
 
-    uint64_t* ks; uint32_t* vs;
-    int rc = sort_pairs_u64_u32(k0, k1, v0, v1, (int)R, end_bit, b + BL.sort_hist, stream, &ks, &vs);
+    uint32_t* ks; uint32_t* vs;
+    int rc = sort_pairs_u32_u32(k0, k1, v0, v1, (int)R, end_bit, b + BL.sort_hist, stream, &ks, &vs);
     if (rc) return rc;
-    if (ks != keys_main || vs != vals_main) return R3DGW_ERR_BAD_ARG;   // internal invariant
+    if (ks != tk_main || vs != vals_main) return R3DGW_ERR_BAD_ARG;   // internal invariant
 
     {
         ProfScope ps(KID_RANGES, stream);
         ranges_gather_kernel<<<(R + 255) / 256, 256, 0, stream>>>(
-            (int)R, keys_main, vals_main, (const float2*)(g + GL.means2D), (const float4*)(g + GL.conic_opacity),
+            (int)R, tk_main, vals_main, (const float2*)(g + GL.means2D), (const float4*)(g + GL.conic_opacity),
             (uint2*)(b + BL.ranges), (float4*)(b + BL.splats), (float4*)(b + BL.splats) + R, gx);
     }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_materialize_sorted_keys(int P, int R, int width, int height, const char* geom_buffer, char* binning_buffer,
+                                  void* stream_) {
+    if (P < 0 || R < 0 || width <= 0 || height <= 0 || !geom_buffer || !binning_buffer) return R3DGW_ERR_BAD_ARG;
+    if (R == 0) return 0;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    r3dgw_geom_layout GL; geom_layout(P, 0, &GL);      // depths precede the SH-dependent fields
+    r3dgw_binning_layout BL; binning_layout(R, width, height, &BL);
+    materialize_keys_kernel<<<(R + 255) / 256, 256, 0, stream>>>(
+        R, (const uint32_t*)(binning_buffer + BL.point_list_keys_alt), (const uint32_t*)(binning_buffer + BL.point_list),
+        (const float*)(geom_buffer + GL.depths), (uint64_t*)(binning_buffer + BL.point_list_keys));
     R3DGW_LAUNCH_CHECK();
     return 0;
 }

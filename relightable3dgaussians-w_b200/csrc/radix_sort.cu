@@ -193,14 +193,26 @@ __global__ void __launch_bounds__(OS_THREADS) onesweep_pass_kernel(
 
         uint32_t excl = 0;
         if (tile > 0) {
+            // look back over the predecessors' (flag, count) words, LB of them in flight per step: the walk is a
+            // chain of dependent L2 round trips (~0.5 us each), which bounds a pass over a small array
+            // (the P-sized depth sort: 245 tiles) long before bandwidth does
+            constexpr int LB = 4;
             int j = (int)tile - 1;
-            while (true) {
-                unsigned long long w = os_status_load(status + (size_t)j * SORT_RADIX + d);
-                unsigned flag = (unsigned)(w >> 32);
-                if (flag == 0) continue;
-                excl += (uint32_t)w;
-                if (flag == 2) break;
-                --j;
+            bool done = false;
+            while (!done) {
+                unsigned long long w[LB];
+#pragma unroll
+                for (int u = 0; u < LB; ++u)
+                    w[u] = (j - u >= 0) ? os_status_load(status + (size_t)(j - u) * SORT_RADIX + d) : (2ull << 32);
+#pragma unroll
+                for (int u = 0; u < LB; ++u) {
+                    if (done) break;
+                    const unsigned flag = (unsigned)(w[u] >> 32);
+                    if (flag == 0) break;              // not published yet: reload from this predecessor
+                    excl += (uint32_t)w[u];
+                    --j;
+                    if (flag == 2) done = true;
+                }
             }
             os_status_store(my, 2u, excl + count);
         }
@@ -252,12 +264,12 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
 
     int hb = (int)std::min<size_t>((size_t)(n + 256 * 16 - 1) / (256 * 16), (size_t)NUM_SMS * 8);
     {
-        ProfScope ps(KID_SORT_HIST, stream);
+        ProfScope ps(g_sort_prof_kid >= 0 ? g_sort_prof_kid : KID_SORT_HIST, stream);
         radix_histogram_kernel<KeyT><<<hb, 256, 0, stream>>>(keys_in, n, sp, hist);
     }
     R3DGW_LAUNCH_CHECK();
     {
-        ProfScope ps(KID_SORT_SCAN, stream);
+        ProfScope ps(g_sort_prof_kid >= 0 ? g_sort_prof_kid : KID_SORT_SCAN, stream);
         radix_scan_kernel<<<sp.n_pass, SORT_RADIX, 0, stream>>>(hist);
     }
     R3DGW_LAUNCH_CHECK();
@@ -271,7 +283,7 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
     uint32_t* vin = vals_in; uint32_t* vout = vals_alt;
     for (int p = 0; p < sp.n_pass; ++p) {
         {
-            ProfScope ps(KID_SORT_PASS, stream);
+            ProfScope ps(g_sort_prof_kid >= 0 ? g_sort_prof_kid : KID_SORT_PASS, stream);
             onesweep_pass_kernel<KeyT><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
                 kin, vin, kout, vout, n, sp.shift[p], sp.mask[p], hist + p * SORT_RADIX, counters + p,
                 status + (size_t)p * status_per_pass);

@@ -134,6 +134,11 @@ class GeometryState:
     def intermediates(self):
         GL, BL = self._geom_layout(), self._binning_layout()
         P, R = self.P, self.R
+        # the pipeline sorts 32-bit tile ids (depth-first binning); the reference's 64-bit keys are rebuilt on demand
+        with torch.cuda.device(self.radii.device):
+            _nat.check(_nat.lib().r3dgw_materialize_sorted_keys(P, R, self.W, self.H, self.geom.data_ptr(),
+                                                                self.binning.data_ptr(), _stream()),
+                       "r3dgw_materialize_sorted_keys")
         tiles = ((self.W + 15) // 16) * ((self.H + 15) // 16)
         out = {
             "depths": self._view(self.geom, GL.depths, P, torch.float32),
@@ -291,7 +296,9 @@ class _BlendFn(torch.autograd.Function):
             mode, cache, img = 2, _alpha_pool["buf"], st.alpha_img
         else:
             img = torch.empty(IL.total, dtype=torch.uint8, device=dev)
-            if _ALPHA_CACHE and st.blend_calls >= 2 and st.R > 0:
+            # record on the second blend over this geometry - or already on the first when the previous geometry was
+            # blended three times or more (a render() loop: this one will be too)
+            if _ALPHA_CACHE and st.R > 0 and (st.blend_calls >= 2 or _alpha_pool["prev_calls"] >= 3):
                 cache = _alpha_pool_get(int(L.r3dgw_alpha_cache_bytes(st.R)), dev)
                 if cache is not None:
                     mode = 1
@@ -364,7 +371,7 @@ _ALPHA_ROUND = 256 << 20
 
 # One grow-only device buffer serves every geometry state in turn (the state that recorded last owns it): a fresh
 # multi-GB cudaMalloc per view costs tens of ms of page-table setup, and R moves a little every training step.
-_alpha_pool = {"buf": None, "owner": None}
+_alpha_pool = {"buf": None, "owner": None, "prev_calls": 0}
 
 
 def _alpha_pool_get(nbytes, device):
@@ -436,6 +443,7 @@ def set_alpha_cache(enabled: bool):
     global _ALPHA_CACHE
     _ALPHA_CACHE = bool(enabled)
     clear_geometry_cache()
+    _alpha_pool["prev_calls"] = 0
     if not enabled:
         _alpha_pool["buf"], _alpha_pool["owner"] = None, None
 
@@ -444,6 +452,8 @@ _cache = {"key": None, "entry": None}
 
 
 def clear_geometry_cache():
+    if _cache["entry"] is not None:
+        _alpha_pool["prev_calls"] = _cache["entry"][0].blend_calls
     _cache["key"] = None
     _cache["entry"] = None
 
@@ -473,6 +483,9 @@ def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, mean
            grad_mode)
     if _CACHE_ENABLED and _cache["key"] == key:
         return _cache["entry"]
+    prev = _cache["entry"]
+    if prev is not None:
+        _alpha_pool["prev_calls"] = prev[0].blend_calls
     box = []
     handles = _GeometryFn.apply(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, box, means2D)
     st = box[0]

@@ -27,7 +27,7 @@ SYMBOLS = [
     "r3dgw_profile_read", "r3dgw_image_loss_workspace_bytes", "r3dgw_ssim_l1_forward", "r3dgw_ssim_l1_backward",
     "r3dgw_masked_l1_forward", "r3dgw_masked_l1_backward", "r3dgw_depth_to_normal_forward",
     "r3dgw_depth_to_normal_backward", "r3dgw_alpha_cache_bytes", "r3dgw_blend_forward_cached",
-    "r3dgw_blend_backward_color_cached",
+    "r3dgw_blend_backward_color_cached", "r3dgw_materialize_sorted_keys",
 ]
 
 
@@ -83,7 +83,7 @@ class Camera(ctypes.Structure):
 class GeomLayout(ctypes.Structure):
     _fields_ = [(n, ctypes.c_size_t) for n in
                 ("depths", "means2D", "conic_opacity", "cov3D", "tiles_touched", "point_offsets",
-                 "rgb", "clamped", "scan_state", "total")]
+                 "rgb", "clamped", "scan_state", "depth_sort", "total")]
 
 
 class BinningLayout(ctypes.Structure):
@@ -133,6 +133,7 @@ def lib():
     L.r3dgw_blend_forward.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp]
     L.r3dgw_blend_forward_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp, ci, vp]
     L.r3dgw_blend_backward_color_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp]
+    L.r3dgw_materialize_sorted_keys.argtypes = [ci, ci, ci, ci, vp, vp, vp]
     L.r3dgw_alpha_cache_bytes.argtypes = [ci]
     L.r3dgw_alpha_cache_bytes.restype = ctypes.c_size_t
     L.r3dgw_blend_backward.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
