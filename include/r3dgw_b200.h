@@ -302,6 +302,31 @@ int r3dgw_depth_to_normal_forward(int H, int W, const float* depth, const float*
 int r3dgw_depth_to_normal_backward(int H, int W, const float* depth, const float* rays, const float* dL_dnormal,
                                    float* dL_ddepth, void* stream);
 
+/* ---- host side of the eval grid on the device -----------------------------------
+ * Replace numpy / cv2 / spaudiopy host code in the reference (paths relative to /root/reference):
+ *   r3dgw_envmap_resize_cubic <- utils/sh_additional_utils.py:48-70 (resize_image -> cv2.resize INTER_CUBIC, the
+ *                                (1000, 500) down-scale of :181-184)
+ *   r3dgw_envmap_sh_project   <- utils/sh_additional_utils.py:176-206 (get_coefficients_from_image: real SH basis
+ *                                of utils/spherical_harmonics.py:148-216 x per-row solid angle, summed per channel)
+ *   r3dgw_sh_rotate_sweep     <- spaudiopy.sph.rotate_sh(F, yaw, pitch, roll, 'real') applied twice per sun angle,
+ *                                eval_with_gt_envmaps.py:95-100 / relit_novel_view.py:72-74 (spaudiopy==0.1.6,
+ *                                environment.yml:239; Ivanic-Ruedenberg recursion)
+ * The source image is EITHER f32 (f32 != NULL) OR u8 (u8 != NULL), [H,W,stride] with stride >= 3 channels per pixel
+ * (extra channels ignored).  For u8 the value is (float)u8 / 255.f and, when boost != 0, values > threshold are
+ * multiplied by scale in f32 (process_environment_map_image, eval_with_gt_envmaps.py:42-49).
+ * Projection: H must equal W/2 (the reference's yres = int(xres/2)); l_max <= 4; coeffs: device f64[(l_max+1)^2, 3];
+ * workspace: r3dgw_envmap_sh_workspace_bytes(H) bytes.  Row partials are reduced in a fixed order.
+ * Rotation sweep: coeffs device f64[n, C] (n = (l_max+1)^2, C <= 4); first_ypr: device f64[3] (yaw, pitch, roll) of
+ * a rotation applied to every entry first, or NULL; angles_ypr: device f64[B,3]; out32 f32[B,n,C] and/or out64
+ * f64[B,n,C] (either may be NULL). */
+size_t r3dgw_envmap_sh_workspace_bytes(int H);
+int r3dgw_envmap_resize_cubic(int H, int W, int stride, const float* f32, const uint8_t* u8, int boost, float threshold,
+                              float scale, int Hd, int Wd, float* dst /* f32[Hd,Wd,3] */, void* stream);
+int r3dgw_envmap_sh_project(int H, int W, int stride, const float* f32, const uint8_t* u8, int boost, float threshold,
+                            float scale, int l_max, char* workspace, double* coeffs, void* stream);
+int r3dgw_sh_rotate_sweep(int l_max, int C, const double* coeffs, const double* first_ypr, int B,
+                          const double* angles_ypr, float* out32, double* out64, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -12,7 +12,7 @@ PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(PKG_ROOT, "csrc")
 LIB_DIR = os.path.join(PKG_ROOT, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libr3dgw_b200.so")
-SOURCES = ["api.cu", "radix_sort.cu", "blend.cu", "knn.cu", "shade.cu", "image_ops.cu"]
+SOURCES = ["api.cu", "radix_sort.cu", "blend.cu", "knn.cu", "shade.cu", "image_ops.cu", "envmap_sh.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
@@ -27,7 +27,8 @@ SYMBOLS = [
     "r3dgw_profile_read", "r3dgw_image_loss_workspace_bytes", "r3dgw_ssim_l1_forward", "r3dgw_ssim_l1_backward",
     "r3dgw_masked_l1_forward", "r3dgw_masked_l1_backward", "r3dgw_depth_to_normal_forward",
     "r3dgw_depth_to_normal_backward", "r3dgw_alpha_cache_bytes", "r3dgw_blend_forward_cached",
-    "r3dgw_blend_backward_color_cached", "r3dgw_materialize_sorted_keys",
+    "r3dgw_blend_backward_color_cached", "r3dgw_materialize_sorted_keys", "r3dgw_envmap_sh_workspace_bytes",
+    "r3dgw_envmap_resize_cubic", "r3dgw_envmap_sh_project", "r3dgw_sh_rotate_sweep",
 ]
 
 
@@ -157,6 +158,12 @@ def lib():
     L.r3dgw_masked_l1_backward.argtypes = [ci, ci, ci, vp, vp, vp, sz, ci, vp, vp, vp, vp]
     L.r3dgw_depth_to_normal_forward.argtypes = [ci, ci, vp, vp, vp, vp]
     L.r3dgw_depth_to_normal_backward.argtypes = [ci, ci, vp, vp, vp, vp, vp]
+    cf = ctypes.c_float
+    L.r3dgw_envmap_sh_workspace_bytes.argtypes = [ci]
+    L.r3dgw_envmap_sh_workspace_bytes.restype = sz
+    L.r3dgw_envmap_resize_cubic.argtypes = [ci, ci, ci, vp, vp, ci, cf, cf, ci, ci, vp, vp]
+    L.r3dgw_envmap_sh_project.argtypes = [ci, ci, ci, vp, vp, ci, cf, cf, ci, vp, vp, vp]
+    L.r3dgw_sh_rotate_sweep.argtypes = [ci, ci, vp, vp, ci, vp, vp, vp, vp]
     L.r3dgw_profile_enable.argtypes = [ci]
     L.r3dgw_profile_enable.restype = None
     L.r3dgw_profile_kernel_name.argtypes = [ci]
@@ -165,7 +172,8 @@ def lib():
     for name in SYMBOLS:
         fn = getattr(L, name)
         if name not in ("r3dgw_version", "r3dgw_launch_count", "r3dgw_knn_workspace_bytes", "r3dgw_profile_enable",
-                        "r3dgw_profile_kernel_name", "r3dgw_image_loss_workspace_bytes", "r3dgw_alpha_cache_bytes"):
+                        "r3dgw_profile_kernel_name", "r3dgw_image_loss_workspace_bytes", "r3dgw_alpha_cache_bytes",
+                        "r3dgw_envmap_sh_workspace_bytes"):
             fn.restype = ci
     _lib = L
     return L

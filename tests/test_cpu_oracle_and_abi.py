@@ -2,6 +2,7 @@
 library's exported symbols (no compute calls - there is no GPU here)."""
 import ctypes
 import glob
+import math
 import os
 import re
 
@@ -150,7 +151,7 @@ def test_product_path_never_imports_oracle():
     pkg = os.path.join(ROOT, "relightable3dgaussians-w_b200")
     for path in glob.glob(os.path.join(pkg, "**", "*.py"), recursive=True):
         src = open(path).read()
-        assert all(w not in src for w in ("raster_oracle", "shade_oracle", "image_oracle", "ref_loader")), path
+        assert all(w not in src for w in ("raster_oracle", "shade_oracle", "image_oracle", "sh_oracle", "ref_loader")), path
 
 
 def test_python_api_surface_and_errors():
@@ -205,3 +206,55 @@ def test_image_oracle_matches_reference_python():
     np.testing.assert_allclose(n.detach().numpy(), z["ref_normal"], rtol=0, atol=1e-6)
     ref = z["ref_d_depth"]
     np.testing.assert_allclose(dm.grad.numpy(), ref, rtol=1e-4, atol=1e-5 * np.abs(ref).max())
+
+
+# ---- eval-grid host side: oracle vs the reference's own numpy (tests/golden/make_envmap_golden.py) ----
+def test_envmap_sh_oracle_matches_reference_python():
+    import sh_oracle as so
+    z = np.load(os.path.join(GOLD, "envmap_sh.npz"))
+    for name in "abcde":
+        c = so.project(z[name + "_img"], int(z[name + "_lmax"]))
+        np.testing.assert_allclose(c, z[name + "_coeffs"], rtol=0, atol=1e-13 * np.abs(z[name + "_coeffs"]).max())
+    c = so.project(so.scale_bright(z["u8_img"], 10, 0.999), 4)
+    np.testing.assert_allclose(c, z["u8_coeffs"], rtol=0, atol=1e-13 * np.abs(z["u8_coeffs"]).max())
+    # resize rule (cv2 INTER_CUBIC restated in f32; cv2's SIMD accumulation order differs in the last bits)
+    r = so.resize_cubic(so.synth_envmap(96, 0.3), 40, 20)
+    np.testing.assert_allclose(r, z["resized_pixels"], rtol=0, atol=2e-6 * np.abs(z["resized_pixels"]).max())
+    for key, w, ph, l, rw in (("big", 1200, 0.1, 4, None), ("rw", 300, 0.2, 3, 128)):
+        c = so.coefficients_from_image(so.synth_envmap(w, ph), l, rw)
+        np.testing.assert_allclose(c, z[key + "_coeffs"], rtol=0, atol=1e-6 * np.abs(z[key + "_coeffs"]).max())
+
+
+def test_sh_rotation_oracle_properties():
+    """spaudiopy is absent (parity unpinned, oracle/sh_oracle.py header): the recursion is anchored on what a real-SH
+    rotation must satisfy."""
+    import sh_oracle as so
+    rng = np.random.default_rng(5)
+    d = rng.normal(size=(300, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    Y = so.real_sh_acn(4, d)
+    for ypr in ((0.3, -0.7, 1.1), (0.0, 0.0, -math.pi / 2), (2.0, 0.0, 0.0), (0.0, 1.3, 0.0)):
+        D = so.sh_rotation_matrix(4, *ypr)
+        R = so.rotation_euler(*ypr)
+        np.testing.assert_allclose(D @ D.T, np.eye(25), atol=1e-13)
+        np.testing.assert_allclose(D[1:4, 1:4], R[np.ix_([1, 2, 0], [1, 2, 0])], atol=0)
+        np.testing.assert_allclose(so.real_sh_acn(4, d @ R), Y @ D, atol=1e-12)      # Y(R^T d) = D^T Y(d)
+    # homomorphism: two yaw rotations compose, and rotate_sh chains like the reference's two calls
+    Da, Db = so.sh_rotation_matrix(4, 0.4, 0, 0), so.sh_rotation_matrix(4, 0.9, 0, 0)
+    np.testing.assert_allclose(Da @ Db, so.sh_rotation_matrix(4, 1.3, 0, 0), atol=1e-13)
+    F = rng.normal(size=(3, 25))
+    np.testing.assert_allclose(so.rotate_sh(so.rotate_sh(F, 0.4, 0, 0), 0.9, 0, 0), so.rotate_sh(F, 1.3, 0, 0), atol=1e-13)
+    np.testing.assert_allclose(so.rotate_sh(F, 0, 0, 0), F, atol=0)
+    sweep = so.eval_grid_rotations(F.T, (0.0, 0.0, -math.pi / 2), [[0.5, 0, 0], [1.0, 0, 0]])
+    assert sweep.shape == (2, 25, 3) and sweep.dtype == np.float32
+    np.testing.assert_allclose(np.linalg.norm(sweep[0]), np.linalg.norm(F), rtol=1e-6)
+
+
+def test_envmap_api_surface_and_errors():
+    from r3dgw_b200 import envmap_sh as E
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only behaviour")
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        E.get_coefficients_from_image(np.zeros((4, 8, 3), np.float32), 2)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        E.rotate_sh(np.zeros((3, 25)), 0.1, 0.2, 0.3)
