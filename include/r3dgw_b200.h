@@ -181,7 +181,9 @@ int r3dgw_blend_backward_color_cached(
     const char* binning_buffer, const char* image_buffer,
     const float* alpha_cache,
     const float* dL_dpixels,   /* f32[C,H,W] */
-    float* dL_dfeatures,       /* f32[P,C], accumulated */
+    float* dL_dfeatures,       /* f32[P,grad_stride], accumulated */
+    int grad_stride,           /* floats per Gaussian row of dL_dfeatures: C, or 4 (16-B aligned rows: the C sums of a
+                                * (warp, Gaussian) pair leave as ONE 16-byte reduction instead of C 4-byte ones) */
     void* stream);
 
 /* K6+K7 fused: conic/mean2D gradients -> means3D, cov3D, scales, rotations (and SH).

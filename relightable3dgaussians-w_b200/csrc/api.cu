@@ -55,7 +55,7 @@ int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4*
                             float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream);
 int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
                                          const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
-                                         float* dL_dfeatures, cudaStream_t stream);
+                                         float* dL_dfeatures, int grad_stride, cudaStream_t stream);
 int sort_num_passes(int end_bit);
 
 static inline int pre_blocks(int P) { return (P + PRE_THREADS - 1) / PRE_THREADS; }
@@ -348,7 +348,7 @@ int r3dgw_blend_forward(int P, int R, int C, const r3dgw_camera* cam, const char
 
 int r3dgw_blend_backward_color_cached(int P, int R, int C, const r3dgw_camera* cam, const char* binning_buffer,
                                       const char* image_buffer, const float* alpha_cache, const float* dL_dpixels,
-                                      float* dL_dfeatures, void* stream_) {
+                                      float* dL_dfeatures, int grad_stride, void* stream_) {
     if (!cam || !binning_buffer || !image_buffer || !dL_dpixels || !dL_dfeatures || R < 0 || P < 0) return R3DGW_ERR_BAD_ARG;
     if (R == 0) return 0;
     if (!alpha_cache) return R3DGW_ERR_BAD_ARG;
@@ -360,7 +360,7 @@ int r3dgw_blend_backward_color_cached(int P, int R, int C, const r3dgw_camera* c
     const float4* A = (const float4*)(binning_buffer + BL.splats);
     return blend_backward_color_cached_dispatch(C, grid, (const uint2*)(binning_buffer + BL.ranges), A + R, W, H,
                                                 (const uint32_t*)(image_buffer + IL.n_contrib), alpha_cache,
-                                                dL_dpixels, dL_dfeatures, stream);
+                                                dL_dpixels, dL_dfeatures, grad_stride, stream);
 }
 
 int r3dgw_blend_backward(int P, int R, int C, const r3dgw_camera* cam, const char* geom_buffer,

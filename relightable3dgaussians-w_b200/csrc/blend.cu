@@ -17,6 +17,7 @@
 //  * backward starts at the tile's deepest contributor instead of the end of the list.
 // Every decision (power > 0, alpha < 1/255, T*(1-alpha) < 1e-4) is evaluated with the reference's
 // expression trees so that n_contrib is bit-identical and colours agree to rounding.
+#include <stdlib.h>
 #include "common.cuh"
 #include "warp_reduce.cuh"
 
@@ -612,30 +613,36 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
 // dL_dfeatures == NULL), instead of once per call.
 // -------------------------------------------------------------------------------------------------
 constexpr int BWDC_BATCH = 256;
-template <int C>
+template <int C, int WROWS>
 struct BwdColorSmem {
     float4 B[2][BWDC_BATCH];
     uint16_t list[TILE_PIX / 32][BWDC_BATCH];
-    // per warp: the blend weights alpha*T of up to 32 pending splats x 32 pixels (row padded to 33: both the
+    // per warp: the blend weights alpha*T of up to WROWS pending splats x 32 pixels (row padded to 33: both the
     // row-wise stores and the column-wise reads are bank-conflict free), their list positions, and the warp's
-    // 32 pixel gradients.  The per-splat reduction over pixels is then W[32x32] . D[32xC], done by 32 lanes at once
-    // (~5 issue slots per splat) instead of a shuffle butterfly per splat (~25); each lane then issues the C
-    // global REDs of its splat (on average 1.6 warps of a tile touch a splat, so parking the partial sums per tile
-    // first would save few atomics and cost a second block barrier per round).
-    float W[TILE_PIX / 32][32][33];
-    uint16_t Wj[TILE_PIX / 32][32];
+    // 32 pixel gradients.  The per-splat reduction over pixels is then W[WROWS x 32] . D[32 x C]: 32 / WROWS lanes
+    // share a row (each sums its slice of the pixels, one shuffle step per halving joins them), ~5 issue slots per
+    // splat instead of a shuffle butterfly per splat (~25); the row's first lane then issues the reduction of its
+    // splat (on average 1.6 warps of a tile touch a splat, so parking the partial sums per tile first would save
+    // few atomics and cost a second block barrier per round).  WROWS = 16 keeps the CTA at 33.6 KB (6 per SM).
+    float W[TILE_PIX / 32][WROWS][33];
+    uint16_t Wj[TILE_PIX / 32][WROWS];
     float4 D[TILE_PIX / 32][32];
     uint32_t red[TILE_PIX / 32];
     uint64_t bar[2];
 };
 
-template <int C>
+// one 16-byte reduction per (warp, splat) when the gradient rows are padded to 4 floats (sm_90+: red.v4.f32)
+__device__ __forceinline__ void red_add_v4(float* dst, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <int C, int DEPTH, int WROWS, bool VEC>
 __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatB, int W, int H,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
     const float* __restrict__ dL_dpixels, float* __restrict__ dL_dfeatures) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    BwdColorSmem<C>& s = *reinterpret_cast<BwdColorSmem<C>*>(smem_raw);
+    BwdColorSmem<C, WROWS>& s = *reinterpret_cast<BwdColorSmem<C, WROWS>*>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned lx, ly;
     tile_pixel(tid, lx, ly);
@@ -702,11 +709,14 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
         // reduce the pending rows over the 32 pixels: lane l owns row l and issues its splat's C atomics
         auto reduce_rows = [&](int n) {
             __syncwarp();
-            if ((int)lane < n) {
-                float o[4] = {0.f, 0.f, 0.f, 0.f};
-                const float* wrow = s.W[warp][lane];
+            constexpr int PARTS = 32 / WROWS;          // lanes per row: each sums 32 / PARTS pixels
+            const int row = (int)lane % WROWS, part = (int)lane / WROWS;
+            float o[4] = {0.f, 0.f, 0.f, 0.f};
+            if (PARTS > 1 || row < n) {
+                const float* wrow = s.W[warp][row];
 #pragma unroll 8
-                for (int p = 0; p < 32; ++p) {
+                for (int k = 0; k < 32 / PARTS; ++k) {
+                    const int p = part * (32 / PARTS) + k;
                     const float wv = wrow[p];
                     const float4 d = s.D[warp][p];
                     o[0] = fmaf(wv, d.x, o[0]);
@@ -714,30 +724,42 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
                     if (C > 2) o[2] = fmaf(wv, d.z, o[2]);
                     if (C > 3) o[3] = fmaf(wv, d.w, o[3]);
                 }
-                const uint32_t id = __float_as_uint(s.B[buf][s.Wj[warp][lane]].w);
-                float* dst = dL_dfeatures + (size_t)id * C;
+            }
+            if (PARTS > 1) {
 #pragma unroll
-                for (int ch = 0; ch < C; ++ch) atomicAdd(dst + ch, o[ch]);
+                for (int ch = 0; ch < C; ++ch)
+#pragma unroll
+                    for (int off = WROWS; off < 32; off <<= 1) o[ch] += __shfl_xor_sync(0xffffffffu, o[ch], off);
+            }
+            if (part == 0 && row < n) {
+                const uint32_t id = __float_as_uint(s.B[buf][s.Wj[warp][row]].w);
+                if (VEC) {
+                    red_add_v4(dL_dfeatures + (size_t)id * 4, o[0], o[1], o[2], o[3]);
+                } else {
+                    float* dst = dL_dfeatures + (size_t)id * C;
+#pragma unroll
+                    for (int ch = 0; ch < C; ++ch) atomicAdd(dst + ch, o[ch]);
+                }
             }
             __syncwarp();
         };
-        for (int g0 = 0; g0 < nsurv; g0 += CACHED_DEPTH) {
-            int js[CACHED_DEPTH];
-            float al[CACHED_DEPTH];
+        for (int g0 = 0; g0 < nsurv; g0 += DEPTH) {
+            int js[DEPTH];
+            float al[DEPTH];
 #pragma unroll
-            for (int u = 0; u < CACHED_DEPTH; ++u) {
+            for (int u = 0; u < DEPTH; ++u) {
                 js[u] = (g0 + u < nsurv) ? (int)list[g0 + u] : -1;
                 al[u] = (js[u] >= 0) ? __ldcs(rows + (size_t)js[u] * TILE_PIX) : 0.f;
             }
 #pragma unroll
-            for (int u = 0; u < CACHED_DEPTH; ++u) {
+            for (int u = 0; u < DEPTH; ++u) {
                 const float alpha = al[u];
                 if (!__any_sync(0xffffffffu, alpha > 0.f)) continue;
                 s.W[warp][pos][lane] = alpha * T;     // 0 for pixels that did not take the splat
                 T = T * (1 - alpha);
                 if (lane == 0) s.Wj[warp][pos] = (uint16_t)js[u];
-                if (++pos == 32) {
-                    reduce_rows(32);
+                if (++pos == WROWS) {
+                    reduce_rows(WROWS);
                     pos = 0;
                 }
             }
@@ -746,29 +768,43 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
     }
 }
 
-template <int C>
+template <int C, int DEPTH, int WROWS, bool VEC>
 static int launch_backward_color_cached(dim3 grid, const uint2* ranges, const float4* B, int W, int H,
                                         const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
                                         float* dL_dfeatures, cudaStream_t stream) {
-    const int smem = (int)sizeof(BwdColorSmem<C>);
-    R3DGW_CUDA_TRY(cudaFuncSetAttribute(blend_backward_color_cached_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int smem = (int)sizeof(BwdColorSmem<C, WROWS>);
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute(blend_backward_color_cached_kernel<C, DEPTH, WROWS, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     {
         ProfScope ps(KID_BLEND_BWD_COLOR, stream);
-        blend_backward_color_cached_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, B, W, H, n_contrib, alpha_cache, dL_dpix,
+        blend_backward_color_cached_kernel<C, DEPTH, WROWS, VEC><<<grid, TILE_PIX, smem, stream>>>(ranges, B, W, H, n_contrib, alpha_cache, dL_dpix,
                                                                               dL_dfeatures);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;
 }
 
+template <int C>
+static int launch_backward_color_cached_depth(dim3 grid, const uint2* ranges, const float4* B, int W, int H,
+                                              const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
+                                              float* dL_dfeatures, bool vec, cudaStream_t stream) {
+    // measured on B200 (config B, 5 calls per step): rows-per-reduce 32 / 8 loads in flight 2.27 ms, 16 / 8 2.05 ms
+    // (33.6 KB of smem instead of 50.7 KB: 6 CTAs per SM), deeper load queues (12, 16) no faster; with 16-byte
+    // reductions into padded gradient rows 1.98 ms
+    return vec ? launch_backward_color_cached<C, 8, 16, true>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream)
+               : launch_backward_color_cached<C, 8, 16, false>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+}
+
 int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
                                          const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
-                                         float* dL_dfeatures, cudaStream_t stream) {
+                                         float* dL_dfeatures, int grad_stride, cudaStream_t stream) {
+    if (grad_stride != C && grad_stride != 4) return R3DGW_ERR_BAD_ARG;
+    const bool vec = grad_stride == 4 && (reinterpret_cast<uintptr_t>(dL_dfeatures) & 15) == 0;
+    if (grad_stride == 4 && C < 4 && !vec) return R3DGW_ERR_BAD_ARG;
     switch (C) {
-        case 1: return launch_backward_color_cached<1>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
-        case 2: return launch_backward_color_cached<2>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
-        case 3: return launch_backward_color_cached<3>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
-        case 4: return launch_backward_color_cached<4>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+        case 1: return launch_backward_color_cached_depth<1>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
+        case 2: return launch_backward_color_cached_depth<2>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
+        case 3: return launch_backward_color_cached_depth<3>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
+        case 4: return launch_backward_color_cached_depth<4>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
         default: return R3DGW_ERR_UNSUPPORTED;
     }
 }

@@ -335,12 +335,16 @@ class _BlendFn(torch.autograd.Function):
         m2_ok = ctx.means2D_is_ref or not ctx.needs_input_grad[4]
         if (_DEFER_BWD and cache is not None and not ctx.use_sh and C <= 4 and st.R > 0
                 and ((geo_needed and m2_ok) or (not geo_needed and not ctx.needs_input_grad[4]))):
-            dfeat = torch.zeros(P, C, dtype=torch.float32, device=dev)
+            # gradient rows padded to 16 B: one vector reduction per (warp, Gaussian) instead of C scalar ones
+            stride = 4 if _GRAD_PAD else C
+            dfeat = torch.zeros(P, stride, dtype=torch.float32, device=dev)
             with torch.cuda.device(dev):
                 rc = L.r3dgw_blend_backward_color_cached(P, st.R, C, ctypes.byref(st.cam), st.binning.data_ptr(),
                                                          img.data_ptr(), cache.data_ptr(), g.data_ptr(),
-                                                         dfeat.data_ptr(), _stream())
+                                                         dfeat.data_ptr(), stride, _stream())
             _nat.check(rc, "r3dgw_blend_backward_color_cached")
+            if stride != C:
+                dfeat = dfeat[:, :C]
             if geo_needed:
                 st.pending.append((feats, bgc, g, img))
             return None, None, None, None, None, dfeat, None, None
@@ -394,6 +398,7 @@ def _alpha_pool_get(nbytes, device):
     return _alpha_pool["buf"]
 
 
+_GRAD_PAD = os.environ.get("R3DGW_GRAD_PAD", "1") != "0"
 _DEFER_BWD = os.environ.get("R3DGW_DEFERRED_BACKWARD", "1") != "0"
 _BWD_CHANNELS = (32, 27, 24, 18, 16, 15, 12, 9, 8, 6, 4, 3, 2, 1)      # channel counts K5 is instantiated for
 

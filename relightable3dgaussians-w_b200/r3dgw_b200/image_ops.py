@@ -12,6 +12,7 @@ sync per call) and return the Python constants 1 / 0; here the same values come 
 gradient, so the step never synchronises.
 """
 import math
+import weakref
 
 import torch
 
@@ -143,9 +144,27 @@ def photometric_loss(image, gt, mask, lambda_dssim):
 
 
 # ---- depth_to_normal ----------------------------------------------------------------------------------------
+_RAY_BASIS = {}     # (transform storage, version, size, fov) -> f32[21]; cameras are constant during training
+
+
 def ray_basis(view):
     """The camera-constant part of depths_to_points (graphics_utils.py:142-155), computed with the same torch ops:
-    f32[21] = intrins.inverse().T (row-major), c2w[:3,:3].T (row-major), rays_o."""
+    f32[21] = intrins.inverse().T (row-major), c2w[:3,:3].T (row-major), rays_o.
+    Memoised per camera: the two `inverse()` calls synchronise the device (LU status check), which the reference
+    pays on every render; the key includes the transform's version counter, so an edited camera is recomputed."""
+    wvt = view.world_view_transform
+    key = (id(wvt), wvt._version, int(view.image_width), int(view.image_height), float(view.FoVx), float(view.FoVy))
+    hit = _RAY_BASIS.get(key)
+    if hit is not None and hit[0]() is wvt:      # the weak reference guards against a recycled id()
+        return hit[1]
+    if len(_RAY_BASIS) >= 8192:
+        _RAY_BASIS.clear()
+    out = _ray_basis_uncached(view)
+    _RAY_BASIS[key] = (weakref.ref(wvt), out)
+    return out
+
+
+def _ray_basis_uncached(view):
     wvt = view.world_view_transform
     c2w = (wvt.T).inverse()
     W, H = view.image_width, view.image_height

@@ -133,7 +133,7 @@ def lib():
                                          vp, vp, vp, vp, vp, vp, vp, ctypes.POINTER(ci), vp]
     L.r3dgw_blend_forward.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp]
     L.r3dgw_blend_forward_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp, ci, vp]
-    L.r3dgw_blend_backward_color_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp]
+    L.r3dgw_blend_backward_color_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, ci, vp]
     L.r3dgw_materialize_sorted_keys.argtypes = [ci, ci, ci, ci, vp, vp, vp]
     L.r3dgw_alpha_cache_bytes.argtypes = [ci]
     L.r3dgw_alpha_cache_bytes.restype = ctypes.c_size_t
