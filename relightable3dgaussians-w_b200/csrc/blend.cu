@@ -363,19 +363,28 @@ constexpr bool BWD_DIRECT = R3DGW_BWD_DIRECT_RED != 0;
 
 // COLOR = false: the geometry-only pass of the deferred drop-in backward (dL/dfeatures already produced per call by
 // blend_backward_color_cached_kernel): 6 reduced values per (warp, splat) instead of 6 + C
-template <int C, int BATCH, bool COLOR = true>
+// QROWS > 0: the six geometry sums of a (warp, splat) pair are not reduced with a shuffle butterfly per splat.  All six
+// are sums over the warp's pixels of ONE per-pixel scalar q = G * dL/dalpha times a polynomial of the pixel offset
+// d = mean - pixel, and with d = (mean - box origin) - (u, v) they are combinations of six moments of q over the
+// box-local integer pixel coordinates: S0, Su, Sv, Suu, Suv, Svv.  Each lane therefore parks only q (one STS);
+// every QROWS splats the warp computes the moments as a small matrix product Q[QROWS x 32] . Phi[32 x 6] with
+// compile-time Phi (32 / QROWS lanes share a row), and the row's first lane turns them into the six gradients.
+// ~10 issue slots per (warp, splat) instead of ~50 (six products + an 11-shuffle halving butterfly).
+template <int C, int BATCH, bool COLOR = true, int QROWS = 0>
 struct BwdSmem {
     static constexpr int NV = 6 + (COLOR ? C : 0);
     float4 A[2][BATCH];
     float4 B[2][BATCH];
     float4 feat[2][BATCH * ChanPad<C>::CP / 4];
     float acc[BWD_DIRECT ? 1 : BWD_WARPS][BWD_DIRECT ? 1 : BATCH * NV];
+    float Q[QROWS > 0 ? BWD_WARPS : 1][QROWS > 0 ? QROWS : 1][33];
+    uint16_t Qj[QROWS > 0 ? BWD_WARPS : 1][QROWS > 0 ? QROWS : 1];
     uint32_t mask[BWD_WARPS][(BATCH + 31) / 32];
     uint32_t red[BWD_WARPS];
     uint64_t bar[2];
 };
 
-template <int C, int BATCH, bool COLOR>
+template <int C, int BATCH, bool COLOR, int QROWS>
 __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatA, const float4* __restrict__ splatB,
     int W, int H, const float* __restrict__ bg_color, const float* __restrict__ features,
@@ -384,7 +393,9 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     float* __restrict__ dL_dopacity, float* __restrict__ dL_dfeatures) {
     constexpr int NV = 6 + (COLOR ? C : 0);
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    BwdSmem<C, BATCH, COLOR>& s = *reinterpret_cast<BwdSmem<C, BATCH, COLOR>*>(smem_raw);
+    constexpr bool MOM = QROWS > 0;
+    static_assert(!MOM || !BWD_DIRECT, "the moment reduction parks its results per tile");
+    BwdSmem<C, BATCH, COLOR, QROWS>& s = *reinterpret_cast<BwdSmem<C, BATCH, COLOR, QROWS>*>(smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned lx, ly;
     tile_pixel(tid, lx, ly);
@@ -392,6 +403,8 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
     const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
+    // pixel coordinates of the warp's 8x4 box origin (lane 0's pixel)
+    const float box_x = (float)(blockIdx.x * TILE_X + (warp & 1) * 8), box_y = (float)(blockIdx.y * TILE_Y + (warp >> 1) * 4);
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
     const float T_final = inside ? final_Ts[pix_id] : 0;
@@ -479,6 +492,61 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
             bulk_g2s(s.B[nb], splatB + off, (uint32_t)ncnt * 16u, &s.bar[nb]);
         }
 
+        int qpos = 0;   // pending rows of Q (warp-uniform)
+        auto reduce_q = [&](int n) {
+            if constexpr (MOM) {
+                __syncwarp();
+                constexpr int PARTS = 32 / QROWS, PP = QROWS;      // PP pixels of the box per lane
+                const int row = (int)lane % QROWS, part = (int)lane / QROWS;
+                float S0 = 0.f, Su = 0.f, Sv = 0.f, Suu = 0.f, Suv = 0.f, Svv = 0.f;
+                const float* qrow = &s.Q[warp][row][part * PP];
+#pragma unroll
+                for (int k = 0; k < PP; ++k) {                     // pixel p = part*PP + k: u = p & 7, v = p >> 3
+                    const float q = qrow[k];
+                    const float u = (float)(k & 7), v = (float)(k >> 3);
+                    S0 += q;
+                    if ((k & 7) != 0) { Su = fmaf(q, u, Su); Suu = fmaf(q, u * u, Suu); }
+                    if ((k >> 3) != 0) { Sv = fmaf(q, v, Sv); Svv = fmaf(q, v * v, Svv); }
+                    if ((k & 7) != 0 && (k >> 3) != 0) Suv = fmaf(q, u * v, Suv);
+                }
+                if (PARTS > 1) {
+                    const float vb = (float)(part * (PP / 8));     // rows of the box before this lane's slice
+                    Svv = fmaf(vb * vb, S0, fmaf(2.f * vb, Sv, Svv));
+                    Suv = fmaf(vb, Su, Suv);
+                    Sv = fmaf(vb, S0, Sv);
+#pragma unroll
+                    for (int off = QROWS; off < 32; off <<= 1) {
+                        S0 += __shfl_xor_sync(0xffffffffu, S0, off);
+                        Su += __shfl_xor_sync(0xffffffffu, Su, off);
+                        Sv += __shfl_xor_sync(0xffffffffu, Sv, off);
+                        Suu += __shfl_xor_sync(0xffffffffu, Suu, off);
+                        Suv += __shfl_xor_sync(0xffffffffu, Suv, off);
+                        Svv += __shfl_xor_sync(0xffffffffu, Svv, off);
+                    }
+                }
+                if (part == 0 && row < n) {
+                    const int jj = (int)s.Qj[warp][row];
+                    const float4 a = s.A[buf][jj];
+                    const float4 b = s.B[buf][jj];
+                    const float mx = a.x - box_x, my = a.y - box_y;          // d = (mx - u, my - v)
+                    const float X1 = fmaf(mx, S0, -Su), Y1 = fmaf(my, S0, -Sv);
+                    const float XX = fmaf(mx, fmaf(mx, S0, -2.f * Su), Suu);
+                    const float YY = fmaf(my, fmaf(my, S0, -2.f * Sv), Svv);
+                    const float XY = fmaf(mx, fmaf(my, S0, -Sv), fmaf(-my, Su, Suv));
+                    const float o = b.y;                                     // q = G dL/dalpha; dL/dG G = o q
+                    float* slot = &s.acc[warp][jj * NV];
+                    slot[0] = -o * (a.z * X1 + a.w * Y1) * ddelx_dx;
+                    slot[1] = -o * (b.x * Y1 + a.w * X1) * ddely_dy;
+                    const float ho = -0.5f * o;
+                    slot[2] = ho * XX;
+                    slot[3] = ho * XY;
+                    slot[4] = ho * YY;
+                    slot[5] = S0;
+                    atomicOr(&s.mask[warp][jj >> 5], 1u << (jj & 31));
+                }
+                __syncwarp();
+            }
+        };
         if ((uint32_t)lo < warp_last) {
             // 32 splats at a time, deepest first: lane-parallel footprint cull, then the survivors back to front
             for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
@@ -506,6 +574,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                     }
                     if (__any_sync(0xffffffffu, valid)) {
                         float g[NV];
+                        float qgeo = 0.f;   // MOM: the one geometry scalar of this pixel, G * dL/dalpha
 #pragma unroll
                         for (int q = 0; q < NV; ++q) g[q] = 0.f;
                         if (valid) {
@@ -538,6 +607,8 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                             float dL_dalpha = (sdot - rec_A) * T;
                             last_alpha = alpha;
                             if (bg_nonzero) dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
+                            qgeo = G * dL_dalpha;
+                            if constexpr (!MOM) {
                             const float dL_dG = b.y * dL_dalpha;
                             const float gdx = G * d.x;
                             const float gdy = G * d.y;
@@ -550,8 +621,21 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                             g[3] = hG * gdx * d.y;
                             g[4] = hG * gdy * d.y;
                             g[5] = G * dL_dalpha;
+                            }
                         }
-                        if constexpr (BWD_DIRECT) {
+                        if constexpr (MOM) {
+                            s.Q[warp][qpos][lane] = qgeo;
+                            if (lane == 0) s.Qj[warp][qpos] = (uint16_t)jj;
+                            if constexpr (COLOR) {
+                                float* slot = &s.acc[warp][jj * NV + 6];
+                                warp_reduce_multi<C>(g + 6, lane, [&](int vi, float v) { slot[vi] = v; });
+                                my_mask |= 1u << bit;
+                            }
+                            if (++qpos == QROWS) {
+                                reduce_q(QROWS);
+                                qpos = 0;
+                            }
+                        } else if constexpr (BWD_DIRECT) {
                             const uint32_t id = __float_as_uint(b.w);
                             warp_reduce_multi<NV>(g, lane, [&](int vi, float v) {
                                 float* dst;
@@ -568,10 +652,13 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                         }
                     }
                 }
-                if constexpr (!BWD_DIRECT) {
+                if constexpr (MOM) {
+                    if (lane == 0 && my_mask) atomicOr(&s.mask[warp][c0 >> 5], my_mask);
+                } else if constexpr (!BWD_DIRECT) {
                     if (lane == 0) s.mask[warp][c0 >> 5] = my_mask;
                 }
             }
+            if (qpos > 0) reduce_q(qpos);   // before the flush reads acc and the next round overwrites A / B
         }
         if constexpr (BWD_DIRECT) continue;
         __syncthreads();   // all warps' partial sums parked
@@ -843,16 +930,16 @@ static int launch_forward(dim3 grid, const uint2* ranges, const float4* A, const
     return 0;
 }
 
-template <int C, int BATCH, bool COLOR>
+template <int C, int BATCH, bool COLOR, int QROWS = 0>
 static int launch_backward(dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
                            const float* bg, const float* features, const float* final_T,
                            const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
                            float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream) {
-    const int smem = (int)sizeof(BwdSmem<C, BATCH, COLOR>);
-    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_kernel<C, BATCH, COLOR>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int smem = (int)sizeof(BwdSmem<C, BATCH, COLOR, QROWS>);
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_kernel<C, BATCH, COLOR, QROWS>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     {
         ProfScope ps(COLOR ? KID_BLEND_BWD : KID_BLEND_BWD_GEOM, stream);
-        blend_backward_kernel<C, BATCH, COLOR><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
+        blend_backward_kernel<C, BATCH, COLOR, QROWS><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
                                                                                dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures);
     }
     R3DGW_LAUNCH_CHECK();
@@ -872,6 +959,18 @@ int blend_forward_dispatch(int C, dim3 grid, const uint2* ranges, const float4* 
     }
 }
 
+template <int C>
+static int launch_backward_geom(dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
+                                const float* bg, const float* features, const float* final_T,
+                                const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
+                                float* dL_dconic, float* dL_dopacity, cudaStream_t stream) {
+    // measured on B200 (config B, C = 15): butterfly, BATCH 128: 1.42 ms; moments QROWS 16 / BATCH 128: 1.29 ms
+    // (66 KB of smem, 3 CTAs per SM); QROWS 16 / BATCH 64: 1.18 ms (41 KB, 4 CTAs); QROWS 8 / BATCH 64: 1.19 ms.
+    // With COLOR = true the C colour sums still need their butterfly and the extra smem costs occupancy: no gain
+    // (C = 3: 2.49 -> 2.59 ms fwd+bwd; C = 14: 2.46 -> 2.42 ms), so those kernels keep QROWS = 0.
+    return launch_backward<C, 64, false, 16>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, nullptr, stream);
+}
+
 int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
                             const float* bg, const float* features, const float* final_T,
                             const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
@@ -880,7 +979,7 @@ int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4*
     switch (C) {
 #define R3DGW_BWD_CASE(N, BT) case N: return color \
         ? launch_backward<N, BT, true>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures, stream) \
-        : launch_backward<N, 128, false>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, nullptr, stream);
+        : launch_backward_geom<N>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, stream);
 #define BT_(direct, parked) (BWD_DIRECT ? direct : parked)
         R3DGW_BWD_CASE(1, BT_(256, 128)) R3DGW_BWD_CASE(2, BT_(256, 128)) R3DGW_BWD_CASE(3, BT_(256, 128))
         R3DGW_BWD_CASE(4, BT_(256, 128)) R3DGW_BWD_CASE(6, BT_(256, 128)) R3DGW_BWD_CASE(8, BT_(128, 64))

@@ -1,13 +1,11 @@
 #!/bin/bash
-# kernel-variant sweep for the alpha-cache colour backward
+# moment reduction in the full K5 (COLOR = true): U1 fwd+bwd (C = 3) and the fused single-pass step
 mkdir -p gpurun_out
-: > gpurun_out/variants.jsonl
-for pad in 0 1; do for w in 32 16; do
-  R3DGW_GRAD_PAD=$pad R3DGW_BWDC_WROWS=$w python scripts/diag_kernels.py 10 2>/dev/null | tail -1 >> gpurun_out/variants.jsonl
-done; done
-python - <<'PY'
-import json
-for l in open('gpurun_out/variants.jsonl'):
-    d=json.loads(l); print(d['variant'], 'bwd_color', d.get('blend_backward_color_cached'), 'step', d['_step_ms'], 'ksum', d['_kernel_sum_ms'])
-PY
-python -m pytest tests/test_gpu_raster_vs_reference.py -x -q -m gpu 2>&1 | tail -3
+for q in 0 8 16; do
+  echo "== R3DGW_BWDC_Q=$q"
+  R3DGW_BWDG=3 R3DGW_BWDC_Q=$q DIAG_MODE=fused python scripts/diag_kernels.py 10 2>/dev/null | tail -1 | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('fused: blend_backward', d.get('blend_backward'), 'blend_forward', d.get('blend_forward'), 'step', d['_step_ms'], 'ksum', d['_kernel_sum_ms'])"
+  R3DGW_BWDG=3 R3DGW_BWDC_Q=$q python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-profile 2>/dev/null | tail -1 | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('dropin: step', d['ms_per_step'], 'u1', d['u1_raster_call'], 'fused', d['fused_single_pass']['ms_per_step'])"
+done
+R3DGW_BWDG=3 R3DGW_BWDC_Q=16 python -m pytest tests -x -q -m gpu 2>&1 | tail -3
