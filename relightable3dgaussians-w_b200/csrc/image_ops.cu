@@ -228,41 +228,67 @@ __global__ void __launch_bounds__(IMG_THREADS) ssim_l1_backward_kernel(
 
 // ---- masked L1 (no SSIM): sum |x*m - t*m| and count(m == 1); target may be NULL (zeros) ---------------
 // complement != 0 uses m = 1 - mask (train.py:86: mask = 1 - sky_mask)
+// grid = (blocks per plane, C): no per-element division; four pixels per thread per step through 16-byte loads when
+// the plane is a multiple of 4 and the pointers are aligned (VEC), scalar otherwise.
+template <bool VEC>
 __global__ void __launch_bounds__(IMG_THREADS) masked_l1_forward_kernel(
-    size_t n, size_t plane, const float* __restrict__ x, const float* __restrict__ target,
+    size_t plane, const float* __restrict__ x, const float* __restrict__ target,
     const float* __restrict__ mask, size_t mask_cstride, int complement, float* __restrict__ partials) {
     __shared__ float red[3][IMG_WARPS];
+    const size_t c = blockIdx.y;
+    const float* xc = x + c * plane;
+    const float* tc = target ? target + c * plane : nullptr;
+    const float* mc = mask ? mask + c * mask_cstride : nullptr;
     float accL = 0.f, accN = 0.f;
-    for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < n; i += (size_t)gridDim.x * IMG_THREADS) {
-        float m = 1.f;
-        if (mask) {
-            const size_t c = i / plane;
-            m = mask[c * mask_cstride + (i - c * plane)];
-            if (complement) m = 1.f - m;
-        }
-        const float t = target ? target[i] : 0.f;
-        accL += fabsf(x[i] * m - t * m);
+    auto one = [&](float xv, float tv, float m) {
+        if (complement) m = 1.f - m;
+        accL += fabsf(xv * m - tv * m);
         accN += (m == 1.f) ? 1.f : 0.f;
+    };
+    if (VEC) {
+        const size_t n4 = plane / 4;
+        for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < n4; i += (size_t)gridDim.x * IMG_THREADS) {
+            const float4 xv = reinterpret_cast<const float4*>(xc)[i];
+            const float4 tv = tc ? reinterpret_cast<const float4*>(tc)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 mv = mc ? reinterpret_cast<const float4*>(mc)[i] : make_float4(1.f, 1.f, 1.f, 1.f);
+            one(xv.x, tv.x, mv.x); one(xv.y, tv.y, mv.y); one(xv.z, tv.z, mv.z); one(xv.w, tv.w, mv.w);
+        }
+    } else {
+        for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < plane; i += (size_t)gridDim.x * IMG_THREADS)
+            one(xc[i], tc ? tc[i] : 0.f, mc ? mc[i] : 1.f);
     }
-    block_partials3(0.f, accL, accN, red, partials + (size_t)blockIdx.x * 3);
+    block_partials3(0.f, accL, accN, red, partials + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 3);
 }
 
+template <bool VEC>
 __global__ void __launch_bounds__(IMG_THREADS) masked_l1_backward_kernel(
-    size_t n, size_t plane, const float* __restrict__ x, const float* __restrict__ target,
+    size_t plane, const float* __restrict__ x, const float* __restrict__ target,
     const float* __restrict__ mask, size_t mask_cstride, int complement, const float* __restrict__ sums,
     const float* __restrict__ coef, float* __restrict__ dL_dx) {
     const float k = coef[0] * sums[3];
-    for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < n; i += (size_t)gridDim.x * IMG_THREADS) {
-        float m = 1.f;
-        if (mask) {
-            const size_t c = i / plane;
-            m = mask[c * mask_cstride + (i - c * plane)];
-            if (complement) m = 1.f - m;
-        }
-        const float t = target ? target[i] : 0.f;
-        const float d = x[i] * m - t * m;
+    const size_t c = blockIdx.y;
+    const float* xc = x + c * plane;
+    const float* tc = target ? target + c * plane : nullptr;
+    const float* mc = mask ? mask + c * mask_cstride : nullptr;
+    float* gc = dL_dx + c * plane;
+    auto one = [&](float xv, float tv, float m) {
+        if (complement) m = 1.f - m;
+        const float d = xv * m - tv * m;
         const float sgn = (d > 0.f) ? 1.f : ((d < 0.f) ? -1.f : 0.f);
-        dL_dx[i] = k * sgn * m;
+        return k * sgn * m;
+    };
+    if (VEC) {
+        const size_t n4 = plane / 4;
+        for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < n4; i += (size_t)gridDim.x * IMG_THREADS) {
+            const float4 xv = reinterpret_cast<const float4*>(xc)[i];
+            const float4 tv = tc ? reinterpret_cast<const float4*>(tc)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 mv = mc ? reinterpret_cast<const float4*>(mc)[i] : make_float4(1.f, 1.f, 1.f, 1.f);
+            reinterpret_cast<float4*>(gc)[i] = make_float4(one(xv.x, tv.x, mv.x), one(xv.y, tv.y, mv.y),
+                                                           one(xv.z, tv.z, mv.z), one(xv.w, tv.w, mv.w));
+        }
+    } else {
+        for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < plane; i += (size_t)gridDim.x * IMG_THREADS)
+            gc[i] = one(xc[i], tc ? tc[i] : 0.f, mc ? mc[i] : 1.f);
     }
 }
 
@@ -365,10 +391,16 @@ __global__ void __launch_bounds__(256) depth_to_normal_backward_kernel(int H, in
     dL_ddepth[(size_t)y * W + x] = acc;
 }
 
-static inline int l1_blocks(size_t n) {
-    size_t b = (n + IMG_THREADS * 8 - 1) / (IMG_THREADS * 8);
-    const size_t cap = (size_t)NUM_SMS * 8;
-    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+// blocks per channel plane: 16 pixels per thread, at most NUM_SMS * 8 blocks over all channels (the workspace bound)
+static inline int l1_blocks(size_t plane, int C) {
+    size_t b = (plane + IMG_THREADS * 16 - 1) / (IMG_THREADS * 16);
+    const size_t cap = (size_t)NUM_SMS * 8 / (size_t)C;
+    return (int)(b < 1 ? 1 : (b > cap ? (cap < 1 ? 1 : cap) : b));
+}
+
+static inline bool l1_vec_ok(size_t plane, size_t mask_cstride, const void* x, const void* t, const void* m, const void* g) {
+    auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    return plane % 4 == 0 && mask_cstride % 4 == 0 && al(x) && al(t) && al(m) && al(g);
 }
 
 }  // namespace r3dgw
@@ -420,16 +452,21 @@ int r3dgw_masked_l1_forward(int C, int H, int W, const float* x, const float* ta
                             size_t mask_channel_stride, int complement, char* workspace, float* out, void* stream_) {
     if (C <= 0 || H <= 0 || W <= 0 || !x || !workspace || !out) return R3DGW_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
-    const size_t plane = (size_t)H * W, n = plane * C;
-    const int blocks = l1_blocks(n);
+    const size_t plane = (size_t)H * W;
+    if (C > NUM_SMS * 8) return R3DGW_ERR_UNSUPPORTED;
+    const dim3 grid(l1_blocks(plane, C), C);
     float* partials = reinterpret_cast<float*>(workspace);
     {
         ProfScope ps(KID_MASKED_L1, stream);
-        masked_l1_forward_kernel<<<blocks, IMG_THREADS, 0, stream>>>(n, plane, x, target, mask, mask_channel_stride,
-                                                                     complement, partials);
+        if (l1_vec_ok(plane, mask_channel_stride, x, target, mask, nullptr))
+            masked_l1_forward_kernel<true><<<grid, IMG_THREADS, 0, stream>>>(plane, x, target, mask, mask_channel_stride,
+                                                                             complement, partials);
+        else
+            masked_l1_forward_kernel<false><<<grid, IMG_THREADS, 0, stream>>>(plane, x, target, mask, mask_channel_stride,
+                                                                              complement, partials);
     }
     R3DGW_LAUNCH_CHECK();
-    loss_finalize_kernel<<<1, 256, 0, stream>>>(partials, blocks, out);
+    loss_finalize_kernel<<<1, 256, 0, stream>>>(partials, (int)(grid.x * grid.y), out);
     R3DGW_LAUNCH_CHECK();
     return 0;
 }
@@ -439,12 +476,17 @@ int r3dgw_masked_l1_backward(int C, int H, int W, const float* x, const float* t
                              float* dL_dx, void* stream_) {
     if (C <= 0 || H <= 0 || W <= 0 || !x || !sums || !coef || !dL_dx) return R3DGW_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
-    const size_t plane = (size_t)H * W, n = plane * C;
+    const size_t plane = (size_t)H * W;
+    if (C > NUM_SMS * 8) return R3DGW_ERR_UNSUPPORTED;
+    const dim3 grid(l1_blocks(plane, C), C);
     {
         ProfScope ps(KID_MASKED_L1, stream);
-        masked_l1_backward_kernel<<<l1_blocks(n), IMG_THREADS, 0, stream>>>(n, plane, x, target, mask,
-                                                                           mask_channel_stride, complement, sums, coef,
-                                                                           dL_dx);
+        if (l1_vec_ok(plane, mask_channel_stride, x, target, mask, dL_dx))
+            masked_l1_backward_kernel<true><<<grid, IMG_THREADS, 0, stream>>>(plane, x, target, mask, mask_channel_stride,
+                                                                              complement, sums, coef, dL_dx);
+        else
+            masked_l1_backward_kernel<false><<<grid, IMG_THREADS, 0, stream>>>(plane, x, target, mask, mask_channel_stride,
+                                                                               complement, sums, coef, dL_dx);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;
