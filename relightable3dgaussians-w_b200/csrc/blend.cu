@@ -125,6 +125,11 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     constexpr int CP = ChanPad<C>::CP;
     float T = 1.0f;
     uint32_t last_contributor = 0;
+    // alpha-cache layout: tile t owns rows [range.x * 8, range.y * 8) of 32 floats; warp w's rows are the `total`
+    // rows from range.x * 8 + w * total, filled in the order the warp walks its survivors (row k = its k-th
+    // surviving list entry): every replay streams one contiguous run per warp
+    float* cache_rows = WRITE_CACHE ? alpha_cache + ((size_t)range.x * 8 + (size_t)warp * total) * 32 + lane : nullptr;
+    uint32_t krow = 0;
     float2 Cacc[CP / 2];
 #pragma unroll
     for (int q = 0; q < CP / 2; ++q) Cacc[q] = make_float2(0.f, 0.f);
@@ -194,8 +199,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                         a_eff = alpha;
                     } while (false);
                 }
-                if constexpr (WRITE_CACHE)   // one coalesced 128-B row per surviving (entry, warp)
-                    __stcs(alpha_cache + ((size_t)range.x + base + (uint32_t)j) * TILE_PIX + tid, a_eff);
+                if constexpr (WRITE_CACHE) {   // one coalesced 128-B row per surviving (entry, warp), in walk order
+                    __stcs(cache_rows + (size_t)krow * 32, a_eff);
+                    ++krow;
+                }
             }
             if (__all_sync(0xffffffffu, done)) break;
         }
@@ -273,7 +280,8 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_cached_kernel(
     float2 Cacc[CP / 2];
 #pragma unroll
     for (int q = 0; q < CP / 2; ++q) Cacc[q] = make_float2(0.f, 0.f);
-    const float* my_rows = alpha_cache + (size_t)range.x * TILE_PIX + tid;
+    // this warp's contiguous run of cached rows (layout: blend_forward_kernel); row k = its k-th surviving entry
+    const float* my_rows = alpha_cache + ((size_t)range.x * 8 + (size_t)warp * (range.y - range.x)) * 32 + lane;
 
     for (int i = 0; i < rounds; ++i) {
         const int buf = i & 1;
@@ -311,14 +319,15 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_cached_kernel(
             nsurv += __popc(m);
         }
         __syncwarp();
-        const float* rows = my_rows + (size_t)base * TILE_PIX;
+        const float* rows = my_rows;      // next unread row of the warp's run
+        my_rows += (size_t)nsurv * 32;
         for (int g = 0; g < nsurv; g += CACHED_DEPTH) {
             int js[CACHED_DEPTH];
             float al[CACHED_DEPTH];
 #pragma unroll
             for (int u = 0; u < CACHED_DEPTH; ++u) {
                 js[u] = (g + u < nsurv) ? (int)list[g + u] : -1;
-                al[u] = (js[u] >= 0) ? __ldcs(rows + (size_t)js[u] * TILE_PIX) : 0.f;
+                al[u] = (g + u < nsurv) ? __ldcs(rows + (g + u) * 32) : 0.f;
             }
 #pragma unroll
             for (int u = 0; u < CACHED_DEPTH; ++u) {
@@ -765,7 +774,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
     }
     __syncwarp();
     float T = 1.0f;
-    const float* my_rows = alpha_cache + (size_t)range.x * TILE_PIX + tid;
+    const float* my_rows = alpha_cache + ((size_t)range.x * 8 + (size_t)warp * (range.y - range.x)) * 32 + lane;
 
     for (int i = 0; i < rounds; ++i) {
         const int buf = i & 1;
@@ -791,7 +800,8 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
             nsurv += __popc(m);
         }
         __syncwarp();
-        const float* rows = my_rows + (size_t)base * TILE_PIX;
+        const float* rows = my_rows;      // next unread row of the warp's contiguous run (layout: blend_forward_kernel)
+        my_rows += (size_t)nsurv * 32;
         int pos = 0;   // pending rows of W (warp-uniform)
         // reduce the pending rows over the 32 pixels: lane l owns row l and issues its splat's C atomics
         auto reduce_rows = [&](int n) {
@@ -836,7 +846,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
 #pragma unroll
             for (int u = 0; u < DEPTH; ++u) {
                 js[u] = (g0 + u < nsurv) ? (int)list[g0 + u] : -1;
-                al[u] = (js[u] >= 0) ? __ldcs(rows + (size_t)js[u] * TILE_PIX) : 0.f;
+                al[u] = (g0 + u < nsurv) ? __ldcs(rows + (g0 + u) * 32) : 0.f;
             }
 #pragma unroll
             for (int u = 0; u < DEPTH; ++u) {
