@@ -170,31 +170,49 @@ __global__ void __launch_bounds__(256) shade_forward_kernel(const ShadeParams p,
 
 
 // -------------------------------------------------------------------------------------------------
-// Backward.  Grid-stride over Gaussians; d(env_sh) / d(sky_sh) are accumulated in registers across the
-// thread's Gaussians, reduced over the warp with the halving butterfly, over the CTA through shared
-// memory, and leave the CTA as one atomicAdd per coefficient.
+// Backward.  Grid-stride over Gaussians, one per lane.  d(env_sh) / d(sky_sh) are outer products
+//   d env[k][c] += u_i[k] * g_i[c]   (specular: u = Y_k(r) * lobe(l_k), g = dL/d(spec irradiance);
+//                                     diffuse:  u = irradiance weight w_k(n), g = dL/d(irradiance))
+// so each lane parks its u column and g vector in warp-private shared memory and lane k of the warp sums
+// coefficient k over the warp's 32 Gaussians (a [K x 32] . [32 x 3] product): three live accumulators per lane for
+// the whole loop instead of 87 per thread, no shuffles.  (The first version kept all 87 sums in registers: 255
+// registers + spills, one 256-thread CTA per SM, 0.24 ms at config B; this one: 168 registers, 3 CTAs of 128, 0.22 ms -
+// ncu: 104 M warp instructions, 43 % issue-active at 12 warps/SM, stalled on the loads at the head of the body.
+// Capping at 128 registers for 4 CTAs spills 544 B and is slower, 0.30 ms.)  Warps -> CTA through shared memory, one
+// atomicAdd per coefficient per CTA.
+constexpr int SHADE_BWD_THREADS = 128;
 template <int DEG>
-__global__ void __launch_bounds__(256) shade_backward_kernel(
+__global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
     const ShadeParams p, const float* __restrict__ g_rgb, const float* __restrict__ g_dif,
     const float* __restrict__ g_spc, float* __restrict__ d_pos, float* __restrict__ d_nrm,
     float* __restrict__ d_alb, float* __restrict__ d_kr, float* __restrict__ d_km,
     float* __restrict__ d_env, float* __restrict__ d_sky) {
     constexpr int NSH = (DEG + 1) * (DEG + 1);
     constexpr int NE = NSH * 3;
+    constexpr int NW = SHADE_BWD_THREADS / 32;
+    static_assert(NSH + 4 <= 32, "one lane per env / sky coefficient");
     __shared__ float s_env[NE];
     __shared__ float s_sky[12];
     __shared__ float s_cam[3];
-    __shared__ float s_red[8][NE + 12];
+    __shared__ float s_red[NW][NE + 12];
+    __shared__ float s_U[NW][NSH][33];     // specular columns: Y_k(r_i) * lobe(l_k)
+    __shared__ float s_W[NW][9][33];       // diffuse columns: irradiance weights w_k(n_i)
+    __shared__ float s_S[NW][4][33];       // sky columns: Y_k(view dir_i), k < 4
+    __shared__ float4 s_G[NW][3][32];      // per Gaussian: g_spec, g_irr, g_sky (xyz)
     for (int i = threadIdx.x; i < NE; i += blockDim.x) s_env[i] = p.env_sh[i];
     if (threadIdx.x < 12) s_sky[threadIdx.x] = p.sky_sh ? p.sky_sh[threadIdx.x] : 0.f;
     if (threadIdx.x < 3) s_cam[threadIdx.x] = p.cam_pos[threadIdx.x];
     __syncthreads();
 
-    float acc[NE + 12];
-#pragma unroll
-    for (int k = 0; k < NE + 12; ++k) acc[k] = 0.f;
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float accE[3] = {0.f, 0.f, 0.f};   // lane k < NSH: d env[k][:]; lane NSH + k < NSH + 4: d sky[k][:]
 
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.P; i += gridDim.x * blockDim.x) {
+    for (int i0 = blockIdx.x * blockDim.x; i0 < p.P; i0 += gridDim.x * blockDim.x) {
+        const int i = i0 + (int)threadIdx.x;
+        const bool active = i < p.P;
+        bool any_spec = false, any_sky = false;   // what this lane parked (the warp votes below)
+        float gs[3] = {0.f, 0.f, 0.f}, gi[3] = {0.f, 0.f, 0.f}, gk[3] = {0.f, 0.f, 0.f};
+        if (active) {
         const float3 pos = {p.positions[3 * i], p.positions[3 * i + 1], p.positions[3 * i + 2]};
         const float gr[3] = {g_rgb[3 * i], g_rgb[3 * i + 1], g_rgb[3 * i + 2]};
         float3 gp = {0.f, 0.f, 0.f}, gn = {0.f, 0.f, 0.f};
@@ -212,15 +230,18 @@ __global__ void __launch_bounds__(256) shade_backward_kernel(
                 for (int c = 0; c < 3; ++c) {
                     const float raw = b[0] * s_sky[c] + b[1] * s_sky[3 + c] + b[2] * s_sky[6 + c] + b[3] * s_sky[9 + c] + 0.5f;
                     const float g = raw >= 0.0f ? gr[c] : 0.f;
+                    gk[c] = g;
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        acc[NE + 3 * k + c] += g * b[k];
                         gd.x += g * s_sky[3 * k + c] * bx[k];
                         gd.y += g * s_sky[3 * k + c] * by[k];
                         gd.z += g * s_sky[3 * k + c] * bz[k];
                     }
                 }
                 gp = safe_normalize3_bwd(v, len, gd);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) s_S[warp][k][lane] = b[k];
+                any_sky = true;
             }
         } else {
             const int fi = p.fg_index ? p.fg_index[i] : i;
@@ -291,6 +312,7 @@ __global__ void __launch_bounds__(256) shade_backward_kernel(
                     const float gS = gsv[c] * gamma_bwd(S) + g_sh;
                     if (has_km) gkm += -D[c] * g_sh;
                     const float g_si = (si_raw >= 1e-4f) ? gS * refl : 0.f;
+                    gs[c] = g_si;
                     const float g_refl = gS * si;
                     const float g_F0 = g_refl * fgx;
                     g_fgx += g_refl * F0;
@@ -303,12 +325,14 @@ __global__ void __launch_bounds__(256) shade_backward_kernel(
                     for (int k = 0; k < NSH; ++k) {
                         const int l = sh_band(k);
                         const float e = s_env[3 * k + c];
-                        acc[3 * k + c] += g_si * b[k] * gl[l];
                         ggl[l] += g_si * b[k] * e;
                         const float ce = g_si * gl[l] * e;
                         g_r.x += ce * bx[k]; g_r.y += ce * by[k]; g_r.z += ce * bz[k];
                     }
                 }
+#pragma unroll
+                for (int k = 0; k < NSH; ++k) s_U[warp][k][lane] = b[k] * gl[sh_band(k)];
+                any_spec = true;
 #pragma unroll
                 for (int l = 1; l <= DEG; ++l) gkr += ggl[l] * (-0.3f * (float)(l * (l + 1))) * gl[l];
                 gkr += g_fgx * dfgx_dv + g_fgy * dfgy_dv;
@@ -330,39 +354,70 @@ __global__ void __launch_bounds__(256) shade_backward_kernel(
             for (int c = 0; c < 3; ++c) {
                 galb[c] += gD[c] * irr[c];
                 const float g_irr = (irr_raw[c] >= 1e-4f) ? gD[c] * alb[c] : 0.f;
+                gi[c] = g_irr;
 #pragma unroll
                 for (int k = 0; k < 9; ++k) {
                     const float e = s_env[3 * k + c];
-                    acc[3 * k + c] += g_irr * w[k];
                     gn.x += g_irr * e * wx[k]; gn.y += g_irr * e * wy[k]; gn.z += g_irr * e * wz[k];
                 }
             }
+#pragma unroll
+            for (int k = 0; k < 9; ++k) s_W[warp][k][lane] = w[k];
             if (d_alb) { d_alb[3 * fi] = galb[0]; d_alb[3 * fi + 1] = galb[1]; d_alb[3 * fi + 2] = galb[2]; }
             if (d_kr) d_kr[fi] = gkr;
             if (d_km && p.metalness) d_km[fi] = gkm;
         }
         if (d_pos) { d_pos[3 * i] = gp.x; d_pos[3 * i + 1] = gp.y; d_pos[3 * i + 2] = gp.z; }
         if (d_nrm) { d_nrm[3 * i] = gn.x; d_nrm[3 * i + 1] = gn.y; d_nrm[3 * i + 2] = gn.z; }
+        }   // active
+        // ---- SH-coefficient gradients of this warp's 32 Gaussians: lane k sums coefficient k ----
+        s_G[warp][0][lane] = make_float4(gs[0], gs[1], gs[2], 0.f);
+        s_G[warp][1][lane] = make_float4(gi[0], gi[1], gi[2], 0.f);
+        s_G[warp][2][lane] = make_float4(gk[0], gk[1], gk[2], 0.f);
+        const unsigned m_spec = __ballot_sync(0xffffffffu, any_spec);
+        const unsigned m_sky = __ballot_sync(0xffffffffu, any_sky);
+        const unsigned m_fg = __ballot_sync(0xffffffffu, gi[0] != 0.f || gi[1] != 0.f || gi[2] != 0.f);
+        // columns a lane did not write this iteration hold stale values: their g vector is zero, but 0 * NaN/Inf
+        // must not leak in, so such lanes are skipped through the ballots
+        if (lane < NSH) {
+            for (unsigned m = m_spec; m; m &= m - 1) {
+                const int j = __ffs(m) - 1;
+                const float u = s_U[warp][lane][j];
+                const float4 g = s_G[warp][0][j];
+                accE[0] = fmaf(u, g.x, accE[0]); accE[1] = fmaf(u, g.y, accE[1]); accE[2] = fmaf(u, g.z, accE[2]);
+            }
+            if (lane < 9) {
+                for (unsigned m = m_fg; m; m &= m - 1) {
+                    const int j = __ffs(m) - 1;
+                    const float u = s_W[warp][lane][j];
+                    const float4 g = s_G[warp][1][j];
+                    accE[0] = fmaf(u, g.x, accE[0]); accE[1] = fmaf(u, g.y, accE[1]); accE[2] = fmaf(u, g.z, accE[2]);
+                }
+            }
+        } else if (lane < NSH + 4) {
+            for (unsigned m = m_sky; m; m &= m - 1) {
+                const int j = __ffs(m) - 1;
+                const float u = s_S[warp][lane - NSH][j];
+                const float4 g = s_G[warp][2][j];
+                accE[0] = fmaf(u, g.x, accE[0]); accE[1] = fmaf(u, g.y, accE[1]); accE[2] = fmaf(u, g.z, accE[2]);
+            }
+        }
+        __syncwarp();   // the columns are rewritten by the next iteration
     }
 
-    // ---- reduce the SH-coefficient gradients: warp butterfly -> shared -> one atomic per coefficient
-    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float* slot = s_red[warp];
+    // ---- warps -> CTA through shared memory -> one atomic per coefficient
     constexpr int NT = NE + 12;
-    int off = 0;
+    for (int k = lane; k < NT; k += 32) s_red[warp][k] = 0.f;
+    __syncwarp();
+    if (lane < NSH + 4) {
 #pragma unroll
-    for (int q = 0; q + 32 <= NT; q += 32) { warp_reduce_chunk<32>(acc, q, lane, [&](int vi, float v) { slot[vi] = v; }); off = q + 32; }
-    constexpr int REM = NT % 32;
-    if constexpr ((REM & 16) != 0) { warp_reduce_chunk<16>(acc, off, lane, [&](int vi, float v) { slot[vi] = v; }); off += 16; }
-    if constexpr ((REM & 8) != 0) { warp_reduce_chunk<8>(acc, off, lane, [&](int vi, float v) { slot[vi] = v; }); off += 8; }
-    if constexpr ((REM & 4) != 0) { warp_reduce_chunk<4>(acc, off, lane, [&](int vi, float v) { slot[vi] = v; }); off += 4; }
-    if constexpr ((REM & 2) != 0) { warp_reduce_chunk<2>(acc, off, lane, [&](int vi, float v) { slot[vi] = v; }); off += 2; }
-    if constexpr ((REM & 1) != 0) { warp_reduce_chunk<1>(acc, off, lane, [&](int vi, float v) { slot[vi] = v; }); off += 1; }
+        for (int c = 0; c < 3; ++c) s_red[warp][3 * lane + c] = accE[c];   // sky coefficient k sits at NE + 3k + c = 3 (NSH + k) + c
+    }
     __syncthreads();
     for (int k = threadIdx.x; k < NT; k += blockDim.x) {
         float v = 0.f;
 #pragma unroll
-        for (int wv = 0; wv < 8; ++wv) v += s_red[wv][k];
+        for (int wv = 0; wv < NW; ++wv) v += s_red[wv][k];
         if (v != 0.f) {
             if (k < NE) { if (d_env) atomicAdd(d_env + k, v); }
             else if (d_sky) atomicAdd(d_sky + (k - NE), v);
@@ -420,12 +475,12 @@ extern "C" int r3dgw_shade_backward(const r3dgw_shade_args* a, const float* dL_d
     if (!dL_drgb) return R3DGW_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
     ShadeParams p = to_params(a);
-    const int blocks = std::min((a->P + 255) / 256, NUM_SMS * 4);
+    const int blocks = std::min((a->P + SHADE_BWD_THREADS - 1) / SHADE_BWD_THREADS, NUM_SMS * 12);
     ProfScope ps(KID_SHADE_BWD, stream);
     switch (a->sh_degree) {
-        case 2: shade_backward_kernel<2><<<blocks, 256, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
-        case 3: shade_backward_kernel<3><<<blocks, 256, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
-        default: shade_backward_kernel<4><<<blocks, 256, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
+        case 2: shade_backward_kernel<2><<<blocks, SHADE_BWD_THREADS, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
+        case 3: shade_backward_kernel<3><<<blocks, SHADE_BWD_THREADS, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
+        default: shade_backward_kernel<4><<<blocks, SHADE_BWD_THREADS, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
     }
     R3DGW_LAUNCH_CHECK();
     return 0;
