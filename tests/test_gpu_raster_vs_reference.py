@@ -493,7 +493,8 @@ def test_relit_grid_geometry_reuse_is_exact(native_lib):
     assert st_cached is not None
 
 
-@pytest.mark.parametrize("name,kw", [("small", {}), ("small", dict(W=333, H=211, seed_offset=5)), ("A", {})])
+@pytest.mark.parametrize("name,kw", [("small", {}), ("small", dict(W=333, H=211, seed_offset=5)), ("A", {}),
+                                     ("E", dict(P=20000))])   # E: 4K image, splats of ~38 tiles (moment sums far from the box)
 def test_alpha_cache_replay_is_bit_exact(native_lib, name, kw):
     """Blends #2 (records the alphas) and #3.. (replay them from HBM) over one geometry must produce exactly the image
     and - through the shared final_T / n_contrib - exactly-as-good gradients as the plain kernel, for different channel
