@@ -245,7 +245,7 @@ class Stepper:
             avg_non = torch.mean(depth[(~is_sky) & vis]).detach()
         return loss + LAMBDA["sky_gauss"] * torch.exp(-0.02 * (avg_sky - avg_non))
 
-    def step(self, gt, cam=None, sky2=None, occl1=None):
+    def step(self, gt, cam=None, sky2=None, occl1=None, on_loss=None):
         # optimizer-style in-place touch of every parameter (x *= 1): bumps the tensors' version counters exactly as
         # an optimizer step does, so nothing computed for the previous iteration (geometry cache) can be reused
         with self.torch.no_grad():
@@ -256,6 +256,8 @@ class Stepper:
         occl1 = self.occl1 if occl1 is None else occl1
         out = self.forward(cam, sky2)
         loss = self.loss(out, gt, cam or self.cam, sky2, occl1)
+        if on_loss is not None:
+            on_loss(loss)      # e2e: the loss value starts its way to the host before the backward pass is enqueued
         loss.backward()
         return loss
 
@@ -513,23 +515,61 @@ def main():
     h2d_gbps = (64 << 20) / (ea.elapsed_time(eb) * 1e-3) / 1e9
     del probe_h, probe_d
 
+    loss_ev = torch.cuda.Event()
+
+    def send_loss(loss):
+        h_loss.copy_(loss.detach().reshape(1), non_blocking=True)
+        loss_ev.record()
+
+    # Input pipeline: two device-side input slots; the per-view inputs of step i+1 (GT image, masks, camera) travel on
+    # a copy stream while step i computes, like a prefetching data loader.  Each copy is enqueued at the START of the
+    # step whose event pair times it and is fenced behind an event recorded there, so every step's H2D traffic lies
+    # inside a timed pair (never in the untimed L2-flush gap).
+    copy_stream = torch.cuda.Stream()
+    slots = [dict(gt8=torch.empty_like(d_gt8), view=torch.empty_like(d_view), proj=torch.empty_like(d_proj),
+                  cpos=torch.empty_like(d_cpos), skym8=torch.empty_like(d_skym8), occl8=torch.empty_like(d_occl8))
+             for _ in range(2)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    released = [torch.cuda.Event(), torch.cuda.Event()]
+    pipe = {"k": 0}
+
+    def enqueue_inputs(slot):
+        here = torch.cuda.Event()
+        here.record()
+        copy_stream.wait_event(here)              # not earlier than this point of the compute stream
+        copy_stream.wait_event(released[slot])    # the step that last read this slot is done with it
+        with torch.cuda.stream(copy_stream):
+            b = slots[slot]
+            b["gt8"].copy_(h_gt, non_blocking=True)
+            b["view"].copy_(h_view, non_blocking=True)
+            b["proj"].copy_(h_proj, non_blocking=True)
+            b["cpos"].copy_(h_cpos, non_blocking=True)
+            b["skym8"].copy_(h_skym, non_blocking=True)
+            b["occl8"].copy_(h_occl, non_blocking=True)
+            ready[slot].record(copy_stream)
+
     def step_e2e():
-        d_gt8.copy_(h_gt, non_blocking=True)
-        d_gt = d_gt8.to(torch.float32).mul_(1.0 / 255.0)
-        d_view.copy_(h_view, non_blocking=True)
-        d_proj.copy_(h_proj, non_blocking=True)
-        d_cpos.copy_(h_cpos, non_blocking=True)
-        with torch.no_grad():
+        slot = pipe["k"] & 1
+        pipe["k"] += 1
+        if pipe["k"] == 1:
+            enqueue_inputs(slot)                  # very first call only: nothing was prefetched yet
+        enqueue_inputs(slot ^ 1)                  # the next step's inputs
+        cur = torch.cuda.current_stream()
+        cur.wait_event(ready[slot])
+        b = slots[slot]
+        d_gt = b["gt8"].to(torch.float32).mul_(1.0 / 255.0)
+        with torch.no_grad():                     # the lighting parameters (25x3 + 9x3 floats) ride on the compute stream
             st.env_sh.copy_(h_env, non_blocking=True)
             st.sky_sh.copy_(h_sky, non_blocking=True)
-        c = Camera(W, H, cam.FoVx, cam.FoVy, d_view, d_proj, d_cpos)
-        d_skym8.copy_(h_skym, non_blocking=True)
-        d_occl8.copy_(h_occl, non_blocking=True)
-        loss = st.step(d_gt, c, d_skym8.to(torch.float32), d_occl8.to(torch.float32))
+        c = Camera(W, H, cam.FoVx, cam.FoVy, b["view"], b["proj"], b["cpos"])
+        st.step(d_gt, c, b["skym8"].to(torch.float32), b["occl8"].to(torch.float32), on_loss=send_loss)
+        released[slot].record()
         if bucket is not None:
             bucket.all_reduce(average_over=world)
-        h_loss.copy_(loss.detach().reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()     # the user reads the loss every step
+        # the user reads the loss every step: its 4-byte D2H copy was enqueued right after the forward pass, so the
+        # host waits for that copy only and the backward pass keeps running while the next step is being enqueued
+        loss_ev.synchronize()
+        return float(h_loss[0])
 
     for _ in range(4):          # setup: pinned-copy path and allocator pools for the e2e variant of the step
         step_e2e()
@@ -546,15 +586,18 @@ def main():
                        "mode": args.mode, "views_per_step": world},
             "clocks": clocks, "gpu_launches": int(gpu_launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
-                    "d2h_bytes_per_step": 4, "h2d_gbps_measured": round(h2d_gbps, 2)}}
+                    "d2h_bytes_per_step": 4, "h2d_gbps_measured": round(h2d_gbps, 2),
+                    "loss_read": "this step's loss is copied D2H right after its forward pass and read on the host "
+                                 "before the next step is enqueued (no full-stream sync per step)",
+                    "input_pipeline": "2 input slots; step i+1's GT image / masks / camera are copied on a side stream "
+                                      "while step i computes, fenced inside step i's timed event pair"}}
     if args.impl == "reference":
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                                 "sample": "the reference has no CPU rasterizer: its UNMODIFIED CUDA extension "
                                           "(oracle/_ref, built from /root/reference for sm_100a) + its torch shading "
                                           "graph, same B200, same steps; CPU port figure is in the native arm's line"}
-        line["e2e"] = {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
-                       "d2h_bytes_per_step": 4, "h2d_gbps_measured": round(h2d_gbps, 2)}
+        line["e2e"]["note"] = "same host-buffer protocol as the native arm, through the reference's own extension"
 
     # ---- extras: fwd-only frames/s (U3), single raster call fwd / fwd+bwd (U1) ---------------------------
     def frame(new_view=True):

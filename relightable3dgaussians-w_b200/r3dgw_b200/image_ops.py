@@ -165,13 +165,17 @@ def ray_basis(view):
 
 
 def _ray_basis_uncached(view):
+    # torch.linalg.inv_ex is the LU inverse `Tensor.inverse()` runs, minus its host-side status check (a device sync)
     wvt = view.world_view_transform
-    c2w = (wvt.T).inverse()
+    c2w = torch.linalg.inv_ex(wvt.T)[0]
     W, H = view.image_width, view.image_height
     fx = W / (2 * math.tan(view.FoVx / 2.))
     fy = H / (2 * math.tan(view.FoVy / 2.))
-    intrins = torch.tensor([[fx, 0., W / 2.], [0., fy, H / 2.], [0., 0., 1.0]], dtype=torch.float32, device=wvt.device)
-    return torch.cat([intrins.inverse().T.reshape(-1), c2w[:3, :3].T.reshape(-1), c2w[:3, 3].reshape(-1)]).contiguous()
+    # the reference inverts the intrinsics on the device too; the 3x3 matrix is built and inverted on the host here
+    # (same LAPACK LU in f32, graphics_utils.py:146-149) and uploaded once with the rest of the basis
+    intrins = torch.tensor([[fx, 0., W / 2.], [0., fy, H / 2.], [0., 0., 1.0]], dtype=torch.float32)
+    k_inv_t = torch.linalg.inv_ex(intrins)[0].T.reshape(-1).to(wvt.device, non_blocking=True)
+    return torch.cat([k_inv_t, c2w[:3, :3].T.reshape(-1), c2w[:3, 3].reshape(-1)]).contiguous()
 
 
 class _DepthToNormalFn(torch.autograd.Function):
