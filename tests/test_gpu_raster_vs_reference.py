@@ -33,19 +33,29 @@ def _grad_close(a, b, name, b2=None):
           floor is 1e-3 * scale
       (3) 99.9 % of entries: |a - b| <= 1e-3 |b| + 1e-5 * scale (the elementwise 1e-3 bar up to reference noise)"""
     a, b = a.double(), b.double()
+    # b2: one more run of the reference, or a list of them.  The reference's rotation / scale gradients are heavy-tailed
+    # run to run (scripts/diag_sh_rot.py on B200: ref-vs-ref relative L2 between 1.4e-3 and 1.05e-2 over 6 runs of one
+    # scene, ours-vs-ours <= 2.7e-3, ours-vs-ref 9e-4 .. 6.8e-3), so two samples under-estimate its noise one time in
+    # ten: with several runs the aggregate test is "as close to SOME reference run as the reference runs are to each
+    # other", and the per-entry floor uses the largest deviation seen between them
+    extras = [] if b2 is None else ([t.double() for t in b2] if isinstance(b2, (list, tuple)) else [b2.double()])
+    b2 = extras[0] if extras else None
     scale = b.abs().max().item()
     err = (a - b).abs()
-    l2 = (err.pow(2).sum().sqrt() / b.pow(2).sum().sqrt().clamp_min(1e-30)).item()
+    rel = lambda x, y: ((x - y).pow(2).sum().sqrt() / y.pow(2).sum().sqrt().clamp_min(1e-30)).item()   # noqa: E731
+    l2 = min(rel(a, r) for r in [b] + extras)
     l2_bar = 1e-3
     if name.endswith(("rotations", "scales")):
         # the reference's own two-run relative L2 on these reaches 9.5e-4 (config A, profiles/r01_grad_l2.txt) and is
         # heavy-tailed (a handful of ill-conditioned entries carry it): 3e-3 is ~3x its measured ceiling
         l2_bar = 3e-3
-    if b2 is not None:   # rotations/scales: the reference's own run-to-run L2 deviation reaches 1e-3..4e-2
-        l2_rr = ((b - b2.double()).pow(2).sum().sqrt() / b.pow(2).sum().sqrt().clamp_min(1e-30)).item()
+    if extras:   # rotations/scales: the reference's own run-to-run L2 deviation reaches 1e-3..4e-2
+        refs = [b] + extras
+        l2_rr = max(rel(refs[i], refs[j]) for i in range(len(refs)) for j in range(i))
         l2_bar = max(l2_bar, 3.0 * l2_rr)
     assert l2 <= l2_bar, f"{name}: relative L2 error {l2:.3e} (bar {l2_bar:.3e})"
-    floor = scale * 1e-3 if b2 is None else max(10.0 * (b - b2.double()).abs().max().item(), scale * 5e-3)
+    dev = max((b - r).abs().max().item() for r in extras) if extras else 0.0
+    floor = scale * 1e-3 if not extras else max(10.0 * dev, scale * 5e-3)
     loose = err <= GRAD_RTOL * b.abs() + max(floor, 1e-12)
     strict = err <= GRAD_RTOL * b.abs() + max(scale * 1e-5, 1e-12)
     assert bool(loose.all()), f"{name}: max err {err.max().item():.3e} (scale {scale:.3e}, floor {floor:.3e})"
@@ -125,7 +135,8 @@ def test_forward_backward_vs_reference(mods, name, kw, bgv):
 
     dgr.clear_geometry_cache()
     c_ref, r_ref, g_ref = run(ref)
-    _, _, g_ref2 = run(ref)          # second run of the reference: its own atomic-order noise calibrates the floor
+    g_more = [run(ref)[2] for _ in range(3)]   # more runs of the reference: its own atomic-order noise sets the bar
+    g_ref2 = [[g[k] for g in g_more] for k in range(len(g_ref))]
     c_new, r_new, g_new = run(dgr)
     assert torch.equal(r_ref, r_new)
     assert (c_ref - c_new).abs().max().item() <= IMG_TOL
@@ -203,7 +214,8 @@ def test_six_call_render_pattern_gradient_sum(mods):
     dgr.clear_geometry_cache()
     launches0 = 0
     i_ref, g_ref = run(ref)
-    _, g_ref2 = run(ref)
+    g_more = [run(ref)[1] for _ in range(3)]
+    g_ref2 = [[g[k] for g in g_more] for k in range(len(g_ref))]
     i_new, g_new = run(dgr)
     for a, b in zip(i_new, i_ref):
         assert (a - b).abs().max().item() <= IMG_TOL
@@ -267,7 +279,8 @@ def test_render_mirror_dropin_vs_fused_vs_reference(mods):
         return {k: out[k].detach() for k in keys + ("alpha",)}, grads, out["radii"]
 
     o_ref, g_ref, r_ref = run("ref")
-    _, g_ref2, _ = run("ref")
+    g_more = [run("ref")[1] for _ in range(3)]
+    g_ref2 = [[g[k] for g in g_more] for k in range(len(g_ref))]
     for kind in ("dropin", "fused"):
         o, g, r = run(kind)
         assert torch.equal(r, r_ref)
@@ -381,7 +394,8 @@ def test_sh_colours_path_vs_reference(mods, deg):
 
     dgr.clear_geometry_cache()
     i_r, r_r, g_r = run(ref)
-    _, _, g_r2 = run(ref)
+    g_more = [run(ref)[2] for _ in range(3)]
+    g_r2 = [[g[k] for g in g_more] for k in range(len(g_r))]
     i_n, r_n, g_n = run(dgr)
     assert torch.equal(r_r, r_n)
     assert (i_r - i_n).abs().max().item() <= IMG_TOL
