@@ -229,15 +229,17 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
 // the same operations as blend_forward_kernel, so the output is bit-identical to the uncached kernel.
 // final_T / n_contrib are the producing pass's (identical for every feature set) and are only read.
 // -------------------------------------------------------------------------------------------------
+constexpr int CACHED_DEPTH = 8;
 template <int C>
 struct CachedSmem {
     float4 B[2][FWD_BATCH];
     float4 feat[2][FWD_BATCH * ChanPad<C>::CP / 4];
-    uint16_t list[TILE_PIX / 32][FWD_BATCH];   // per warp: this round's entries that touch its 8x4 footprint
+    // per warp: this round's entries that touch its 8x4 footprint; padded by the prefetch depth so the last group can
+    // load its list slots unconditionally (a slot past nsurv is only ever paired with alpha = 0)
+    uint16_t list[TILE_PIX / 32][FWD_BATCH + CACHED_DEPTH];
     uint32_t red[TILE_PIX / 32];
     uint64_t bar[2];
 };
-constexpr int CACHED_DEPTH = 8;
 
 template <int C>
 __global__ void __launch_bounds__(TILE_PIX) blend_forward_cached_kernel(
@@ -326,7 +328,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_cached_kernel(
             float al[CACHED_DEPTH];
 #pragma unroll
             for (int u = 0; u < CACHED_DEPTH; ++u) {
-                js[u] = (g + u < nsurv) ? (int)list[g + u] : -1;
+                js[u] = (int)list[g + u];
                 al[u] = (g + u < nsurv) ? __ldcs(rows + (g + u) * 32) : 0.f;
             }
 #pragma unroll
@@ -721,7 +723,7 @@ struct BwdColorSmem {
     // splat (on average 1.6 warps of a tile touch a splat, so parking the partial sums per tile first would save
     // few atomics and cost a second block barrier per round).  WROWS = 16 keeps the CTA at 33.6 KB (6 per SM).
     float W[TILE_PIX / 32][WROWS][33];
-    uint16_t Wj[TILE_PIX / 32][WROWS];
+    uint16_t Wj[TILE_PIX / 32][WROWS];   // LEAN: index into `list` of the row's entry, else the entry itself
     float4 D[TILE_PIX / 32][32];
     uint32_t red[TILE_PIX / 32];
     uint64_t bar[2];
@@ -732,7 +734,20 @@ __device__ __forceinline__ void red_add_v4(float* dst, float a, float b, float c
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-template <int C, int DEPTH, int WROWS, bool VEC>
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void sts_u16(uint32_t addr, uint16_t v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(v) : "memory");
+}
+
+// LEAN: the per-row bookkeeping of the walk trimmed (42 SASS instructions per cached row before, ~29 after).  The W
+// row is stored through a running 32-bit shared address (the compiler rebuilt the address of s.W[warp][pos][lane]
+// from the CTA's shared window on every row: 8 of the 20 instructions of the store), and the row's list entry is not
+// prefetched next to its alpha (8 LDS.U16 + 24 PRMT/MOV per group of 8 for the -1 default): lane 0 records the
+// row's position in the survivor list (a register value) and the reducing lane resolves list -> entry -> id once per
+// row.  Same operations on the same values in the same order: bit-identical partial sums.
+template <int C, int DEPTH, int WROWS, bool VEC, bool LEAN>
 __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatB, int W, int H,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
@@ -829,7 +844,8 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
                     for (int off = WROWS; off < 32; off <<= 1) o[ch] += __shfl_xor_sync(0xffffffffu, o[ch], off);
             }
             if (part == 0 && row < n) {
-                const uint32_t id = __float_as_uint(s.B[buf][s.Wj[warp][row]].w);
+                const uint32_t j = LEAN ? (uint32_t)list[s.Wj[warp][row]] : (uint32_t)s.Wj[warp][row];
+                const uint32_t id = __float_as_uint(s.B[buf][j].w);
                 if (VEC) {
                     red_add_v4(dL_dfeatures + (size_t)id * 4, o[0], o[1], o[2], o[3]);
                 } else {
@@ -840,24 +856,34 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
             }
             __syncwarp();
         };
+        const uint32_t w_base = smem_u32(&s.W[warp][0][lane]), wj_base = smem_u32(&s.Wj[warp][0]);
+        uint32_t w_addr = w_base;   // LEAN: &s.W[warp][pos][lane] as a running shared address
         for (int g0 = 0; g0 < nsurv; g0 += DEPTH) {
             int js[DEPTH];
             float al[DEPTH];
 #pragma unroll
             for (int u = 0; u < DEPTH; ++u) {
-                js[u] = (g0 + u < nsurv) ? (int)list[g0 + u] : -1;
+                if (!LEAN) js[u] = (g0 + u < nsurv) ? (int)list[g0 + u] : -1;
                 al[u] = (g0 + u < nsurv) ? __ldcs(rows + (g0 + u) * 32) : 0.f;
             }
 #pragma unroll
             for (int u = 0; u < DEPTH; ++u) {
                 const float alpha = al[u];
                 if (!__any_sync(0xffffffffu, alpha > 0.f)) continue;
-                s.W[warp][pos][lane] = alpha * T;     // 0 for pixels that did not take the splat
-                T = T * (1 - alpha);
-                if (lane == 0) s.Wj[warp][pos] = (uint16_t)js[u];
+                if (LEAN) {
+                    sts_f32(w_addr, alpha * T);       // 0 for pixels that did not take the splat
+                    w_addr += 33 * 4;
+                    T = T * (1 - alpha);
+                    if (lane == 0) sts_u16(wj_base + 2 * pos, (uint16_t)(g0 + u));
+                } else {
+                    s.W[warp][pos][lane] = alpha * T;
+                    T = T * (1 - alpha);
+                    if (lane == 0) s.Wj[warp][pos] = (uint16_t)js[u];
+                }
                 if (++pos == WROWS) {
                     reduce_rows(WROWS);
                     pos = 0;
+                    w_addr = w_base;
                 }
             }
         }
@@ -865,15 +891,15 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
     }
 }
 
-template <int C, int DEPTH, int WROWS, bool VEC>
+template <int C, int DEPTH, int WROWS, bool VEC, bool LEAN>
 static int launch_backward_color_cached(dim3 grid, const uint2* ranges, const float4* B, int W, int H,
                                         const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
                                         float* dL_dfeatures, cudaStream_t stream) {
     const int smem = (int)sizeof(BwdColorSmem<C, WROWS>);
-    R3DGW_CUDA_TRY(cudaFuncSetAttribute(blend_backward_color_cached_kernel<C, DEPTH, WROWS, VEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_color_cached_kernel<C, DEPTH, WROWS, VEC, LEAN>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     {
         ProfScope ps(KID_BLEND_BWD_COLOR, stream);
-        blend_backward_color_cached_kernel<C, DEPTH, WROWS, VEC><<<grid, TILE_PIX, smem, stream>>>(ranges, B, W, H, n_contrib, alpha_cache, dL_dpix,
+        blend_backward_color_cached_kernel<C, DEPTH, WROWS, VEC, LEAN><<<grid, TILE_PIX, smem, stream>>>(ranges, B, W, H, n_contrib, alpha_cache, dL_dpix,
                                                                               dL_dfeatures);
     }
     R3DGW_LAUNCH_CHECK();
@@ -887,8 +913,13 @@ static int launch_backward_color_cached_depth(dim3 grid, const uint2* ranges, co
     // measured on B200 (config B, 5 calls per step): rows-per-reduce 32 / 8 loads in flight 2.27 ms, 16 / 8 2.05 ms
     // (33.6 KB of smem instead of 50.7 KB: 6 CTAs per SM), deeper load queues (12, 16) no faster; with 16-byte
     // reductions into padded gradient rows 1.98 ms
-    return vec ? launch_backward_color_cached<C, 8, 16, true>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream)
-               : launch_backward_color_cached<C, 8, 16, false>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+    // R3DGW_BWDC_LEAN=0 selects the pre-diet walk (A/B timing only: 0.369 -> 0.333 ms per call at config B)
+    static const bool lean = [] { const char* e = getenv("R3DGW_BWDC_LEAN"); return !(e && e[0] == '0'); }();
+    if (!lean)
+        return vec ? launch_backward_color_cached<C, 8, 16, true, false>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream)
+                   : launch_backward_color_cached<C, 8, 16, false, false>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+    return vec ? launch_backward_color_cached<C, 8, 16, true, true>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream)
+               : launch_backward_color_cached<C, 8, 16, false, true>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
 }
 
 int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
