@@ -724,7 +724,7 @@ struct BwdColorSmem {
     // few atomics and cost a second block barrier per round).  WROWS = 16 keeps the CTA at 33.6 KB (6 per SM).
     float W[TILE_PIX / 32][WROWS][33];
     uint16_t Wj[TILE_PIX / 32][WROWS];   // LEAN: index into `list` of the row's entry, else the entry itself
-    float4 D[TILE_PIX / 32][32];
+    float4 D[TILE_PIX / 32][32 * ((C + 3) / 4)];   // the warp's 32 pixel gradients, (C + 3) / 4 channel quads each
     uint32_t red[TILE_PIX / 32];
     uint64_t bar[2];
 };
@@ -748,7 +748,7 @@ __device__ __forceinline__ void sts_u16(uint32_t addr, uint16_t v) {
 // row's position in the survivor list (a register value) and the reducing lane resolves list -> entry -> id once per
 // row.  Same operations on the same values in the same order: bit-identical partial sums.
 template <int C, int DEPTH, int WROWS, bool VEC, bool LEAN>
-__global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
+__global__ void __launch_bounds__(TILE_PIX, C > 4 ? 4 : 1) blend_backward_color_cached_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatB, int W, int H,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
     const float* __restrict__ dL_dpixels, float* __restrict__ dL_dfeatures) {
@@ -781,11 +781,13 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
         mbar_expect_tx(&s.bar[0], cnt * 16u);
         bulk_g2s(s.B[0], splatB + range.x, cnt * 16u, &s.bar[0]);
     }
+    constexpr int CQ = (C + 3) / 4;   // channel quads (C <= 4: one; the fused single-pass call: 16 channels = 4)
     {
-        float dp[4] = {0.f, 0.f, 0.f, 0.f};
+        float dp[4 * CQ];
 #pragma unroll
-        for (int ch = 0; ch < C; ++ch) dp[ch] = inside ? dL_dpixels[(size_t)ch * H * W + pix_id] : 0.f;
-        s.D[warp][lane] = make_float4(dp[0], dp[1], dp[2], dp[3]);
+        for (int ch = 0; ch < 4 * CQ; ++ch) dp[ch] = (ch < C && inside) ? dL_dpixels[(size_t)ch * H * W + pix_id] : 0.f;
+#pragma unroll
+        for (int q = 0; q < CQ; ++q) s.D[warp][lane * CQ + q] = make_float4(dp[4 * q], dp[4 * q + 1], dp[4 * q + 2], dp[4 * q + 3]);
     }
     __syncwarp();
     float T = 1.0f;
@@ -823,18 +825,23 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
             __syncwarp();
             constexpr int PARTS = 32 / WROWS;          // lanes per row: each sums 32 / PARTS pixels
             const int row = (int)lane % WROWS, part = (int)lane / WROWS;
-            float o[4] = {0.f, 0.f, 0.f, 0.f};
+            float o[4 * CQ];
+#pragma unroll
+            for (int ch = 0; ch < 4 * CQ; ++ch) o[ch] = 0.f;
             if (PARTS > 1 || row < n) {
                 const float* wrow = s.W[warp][row];
 #pragma unroll 8
                 for (int k = 0; k < 32 / PARTS; ++k) {
                     const int p = part * (32 / PARTS) + k;
                     const float wv = wrow[p];
-                    const float4 d = s.D[warp][p];
-                    o[0] = fmaf(wv, d.x, o[0]);
-                    if (C > 1) o[1] = fmaf(wv, d.y, o[1]);
-                    if (C > 2) o[2] = fmaf(wv, d.z, o[2]);
-                    if (C > 3) o[3] = fmaf(wv, d.w, o[3]);
+#pragma unroll
+                    for (int q = 0; q < CQ; ++q) {
+                        const float4 d = s.D[warp][p * CQ + q];
+                        o[4 * q] = fmaf(wv, d.x, o[4 * q]);
+                        if (4 * q + 1 < C) o[4 * q + 1] = fmaf(wv, d.y, o[4 * q + 1]);
+                        if (4 * q + 2 < C) o[4 * q + 2] = fmaf(wv, d.z, o[4 * q + 2]);
+                        if (4 * q + 3 < C) o[4 * q + 3] = fmaf(wv, d.w, o[4 * q + 3]);
+                    }
                 }
             }
             if (PARTS > 1) {
@@ -846,8 +853,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_color_cached_kernel(
             if (part == 0 && row < n) {
                 const uint32_t j = LEAN ? (uint32_t)list[s.Wj[warp][row]] : (uint32_t)s.Wj[warp][row];
                 const uint32_t id = __float_as_uint(s.B[buf][j].w);
-                if (VEC) {
-                    red_add_v4(dL_dfeatures + (size_t)id * 4, o[0], o[1], o[2], o[3]);
+                if (VEC) {   // rows of 4 CQ floats (C <= 4: padded to 4; C = 8, 12, 16: dense)
+#pragma unroll
+                    for (int q = 0; q < CQ; ++q)
+                        red_add_v4(dL_dfeatures + (size_t)id * (4 * CQ) + 4 * q, o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
                 } else {
                     float* dst = dL_dfeatures + (size_t)id * C;
 #pragma unroll
@@ -913,6 +922,8 @@ static int launch_backward_color_cached_depth(dim3 grid, const uint2* ranges, co
     // measured on B200 (config B, 5 calls per step): rows-per-reduce 32 / 8 loads in flight 2.27 ms, 16 / 8 2.05 ms
     // (33.6 KB of smem instead of 50.7 KB: 6 CTAs per SM), deeper load queues (12, 16) no faster; with 16-byte
     // reductions into padded gradient rows 1.98 ms
+    // C > 4 (the fused 16-channel call): 4 CTAs per SM by launch bounds (64 registers) 0.75 -> 0.64 ms at C = 16; 4 loads
+    // in flight 0.67 ms, 8 rows per reduce 0.88 ms
     // R3DGW_BWDC_LEAN=0 selects the pre-diet walk (A/B timing only: 0.369 -> 0.333 ms per call at config B)
     static const bool lean = [] { const char* e = getenv("R3DGW_BWDC_LEAN"); return !(e && e[0] == '0'); }();
     if (!lean)
@@ -925,14 +936,19 @@ static int launch_backward_color_cached_depth(dim3 grid, const uint2* ranges, co
 int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
                                          const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
                                          float* dL_dfeatures, int grad_stride, cudaStream_t stream) {
-    if (grad_stride != C && grad_stride != 4) return R3DGW_ERR_BAD_ARG;
-    const bool vec = grad_stride == 4 && (reinterpret_cast<uintptr_t>(dL_dfeatures) & 15) == 0;
-    if (grad_stride == 4 && C < 4 && !vec) return R3DGW_ERR_BAD_ARG;
+    const int padded = (C + 3) / 4 * 4;
+    if (grad_stride != C && grad_stride != padded) return R3DGW_ERR_BAD_ARG;
+    const bool vec = grad_stride == padded && (reinterpret_cast<uintptr_t>(dL_dfeatures) & 15) == 0;
+    if (grad_stride != C && !vec) return R3DGW_ERR_BAD_ARG;
     switch (C) {
         case 1: return launch_backward_color_cached_depth<1>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
         case 2: return launch_backward_color_cached_depth<2>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
         case 3: return launch_backward_color_cached_depth<3>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
         case 4: return launch_backward_color_cached_depth<4>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
+        case 8: return launch_backward_color_cached_depth<8>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
+        case 12: return launch_backward_color_cached_depth<12>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
+        case 15: return launch_backward_color_cached_depth<15>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
+        case 16: return launch_backward_color_cached_depth<16>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, vec, stream);
         default: return R3DGW_ERR_UNSUPPORTED;
     }
 }

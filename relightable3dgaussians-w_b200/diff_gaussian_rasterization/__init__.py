@@ -298,7 +298,11 @@ class _BlendFn(torch.autograd.Function):
             img = torch.empty(IL.total, dtype=torch.uint8, device=dev)
             # record on the second blend over this geometry - or already on the first when the previous geometry was
             # blended three times or more (a render() loop: this one will be too)
-            if _ALPHA_CACHE and st.R > 0 and (st.blend_calls >= 2 or _alpha_pool["prev_calls"] >= 3):
+            # - or when this is a multi-feature call (rasterize_gaussians_features, C > 4) that will be differentiated:
+            # its backward then splits into a colour-only replay + the geometry-only pass (2.47 -> ~1.7 ms at C = 16)
+            split_bwd = (_DEFER_BWD and _SPLIT_FUSED_BWD and C in _BWDC_WIDE and not use_sh
+                         and (ctx.needs_input_grad[5] or ctx.needs_input_grad[1]))
+            if _ALPHA_CACHE and st.R > 0 and (st.blend_calls >= 2 or _alpha_pool["prev_calls"] >= 3 or split_bwd):
                 cache = _alpha_pool_get(int(L.r3dgw_alpha_cache_bytes(st.R)), dev)
                 if cache is not None:
                     mode = 1
@@ -333,10 +337,10 @@ class _BlendFn(torch.autograd.Function):
         cache = st.alpha_cache
         geo_needed = ctx.needs_input_grad[0] or ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
         m2_ok = ctx.means2D_is_ref or not ctx.needs_input_grad[4]
-        if (_DEFER_BWD and cache is not None and not ctx.use_sh and C <= 4 and st.R > 0
+        if (_DEFER_BWD and cache is not None and not ctx.use_sh and (C <= 4 or C in _BWDC_WIDE) and st.R > 0
                 and ((geo_needed and m2_ok) or (not geo_needed and not ctx.needs_input_grad[4]))):
             # gradient rows padded to 16 B: one vector reduction per (warp, Gaussian) instead of C scalar ones
-            stride = 4 if _GRAD_PAD else C
+            stride = 4 if (_GRAD_PAD and C <= 4) else C
             dfeat = torch.zeros(P, stride, dtype=torch.float32, device=dev)
             with torch.cuda.device(dev):
                 rc = L.r3dgw_blend_backward_color_cached(P, st.R, C, ctypes.byref(st.cam), st.binning.data_ptr(),
@@ -400,6 +404,8 @@ def _alpha_pool_get(nbytes, device):
 
 _GRAD_PAD = os.environ.get("R3DGW_GRAD_PAD", "1") != "0"
 _DEFER_BWD = os.environ.get("R3DGW_DEFERRED_BACKWARD", "1") != "0"
+_SPLIT_FUSED_BWD = os.environ.get("R3DGW_SPLIT_FUSED_BACKWARD", "1") != "0"
+_BWDC_WIDE = (8, 12, 16)     # channel counts > 4 the colour-only cached backward is instantiated for (dense 16-B rows)
 _BWD_CHANNELS = (32, 27, 24, 18, 16, 15, 12, 9, 8, 6, 4, 3, 2, 1)      # channel counts K5 is instantiated for
 
 
