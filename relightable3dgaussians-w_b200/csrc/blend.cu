@@ -748,7 +748,7 @@ __device__ __forceinline__ void sts_u16(uint32_t addr, uint16_t v) {
 // row's position in the survivor list (a register value) and the reducing lane resolves list -> entry -> id once per
 // row.  Same operations on the same values in the same order: bit-identical partial sums.
 template <int C, int DEPTH, int WROWS, bool VEC, bool LEAN>
-__global__ void __launch_bounds__(TILE_PIX, C > 4 ? 4 : 1) blend_backward_color_cached_kernel(
+__global__ void __launch_bounds__(TILE_PIX, C > 4 ? 4 : 6) blend_backward_color_cached_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatB, int W, int H,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
     const float* __restrict__ dL_dpixels, float* __restrict__ dL_dfeatures) {
