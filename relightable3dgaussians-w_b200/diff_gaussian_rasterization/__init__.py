@@ -64,7 +64,7 @@ def _f32c(t, device):
 
 
 def _stream():
-    return torch.cuda.current_stream().cuda_stream
+    return _nat.raw_stream()
 
 
 class _Holder:
@@ -135,7 +135,7 @@ class GeometryState:
         GL, BL = self._geom_layout(), self._binning_layout()
         P, R = self.P, self.R
         # the pipeline sorts 32-bit tile ids (depth-first binning); the reference's 64-bit keys are rebuilt on demand
-        with torch.cuda.device(self.radii.device):
+        with _nat.on_device(self.radii.device):
             _nat.check(_nat.lib().r3dgw_materialize_sorted_keys(P, R, self.W, self.H, self.geom.data_ptr(),
                                                                 self.binning.data_ptr(), _stream()),
                        "r3dgw_materialize_sorted_keys")
@@ -189,7 +189,7 @@ def _run_geometry(means3D, opacities, scales, rotations, cov3D_precomp, sh, sett
     st.radii = torch.zeros(st.P, dtype=torch.int32, device=device)
     gh, bh = _Holder(device), _Holder(device)
     R = ctypes.c_int(0)
-    with torch.cuda.device(device):
+    with _nat.on_device(device):
         rc = L.r3dgw_geometry_forward(gh.cb, None, bh.cb, None, st.P, int(settings.sh_degree), M,
                                       ctypes.byref(cam), _ptr(m3), _ptr(shc), _ptr(op), _ptr(sc), _ptr(ro),
                                       _ptr(cv), st.radii.data_ptr(), ctypes.byref(R), _stream())
@@ -253,7 +253,7 @@ class _GeometryFn(torch.autograd.Function):
         drot = flat[12 * P:16 * P].view(P, 4)
         dsh = torch.zeros(ctx.shapes[5], dtype=torch.float32, device=dev) if shc is not None else None
         g_rgb_c = g_rgb.contiguous() if shc is not None else None
-        with torch.cuda.device(dev):
+        with _nat.on_device(dev):
             rc = L.r3dgw_geometry_backward(P, st.sh_degree, st.M, ctypes.byref(st.cam), _ptr(m3), _ptr(shc),
                                            _ptr(sc), _ptr(ro), _ptr(cv), st.radii.data_ptr(),
                                            st.geom.data_ptr(), g_mean2D.data_ptr(), g_conic.data_ptr(),
@@ -306,7 +306,7 @@ class _BlendFn(torch.autograd.Function):
                 cache = _alpha_pool_get(int(L.r3dgw_alpha_cache_bytes(st.R)), dev)
                 if cache is not None:
                     mode = 1
-        with torch.cuda.device(dev):
+        with _nat.on_device(dev):
             rc = L.r3dgw_blend_forward_cached(st.P, st.R, C, ctypes.byref(st.cam), st.geom.data_ptr(),
                                               st.binning.data_ptr(), img.data_ptr(), _ptr(feats), bgc.data_ptr(),
                                               out.data_ptr(), None if cache is None else cache.data_ptr(), mode,
@@ -342,7 +342,7 @@ class _BlendFn(torch.autograd.Function):
             # gradient rows padded to 16 B: one vector reduction per (warp, Gaussian) instead of C scalar ones
             stride = 4 if (_GRAD_PAD and C <= 4) else C
             dfeat = torch.zeros(P, stride, dtype=torch.float32, device=dev)
-            with torch.cuda.device(dev):
+            with _nat.on_device(dev):
                 rc = L.r3dgw_blend_backward_color_cached(P, st.R, C, ctypes.byref(st.cam), st.binning.data_ptr(),
                                                          img.data_ptr(), cache.data_ptr(), g.data_ptr(),
                                                          dfeat.data_ptr(), stride, _stream())
@@ -357,7 +357,7 @@ class _BlendFn(torch.autograd.Function):
         dconic = flat[3 * P:7 * P].view(P, 4)
         dopac = flat[7 * P:8 * P].view(P, 1)
         dfeat = flat[8 * P:].view(P, C)
-        with torch.cuda.device(dev):
+        with _nat.on_device(dev):
             rc = L.r3dgw_blend_backward(P, st.R, C, ctypes.byref(st.cam), st.geom.data_ptr(),
                                         st.binning.data_ptr(), img.data_ptr(),
                                         None if ctx.use_sh else feats.data_ptr(), bgc.data_ptr(), g.data_ptr(),
@@ -441,7 +441,7 @@ def _deferred_geometry_pass(st, dev):
             bgc = torch.cat([e[1].reshape(-1) for e in grp])
             g = torch.cat([e[2] for e in grp], dim=0)
         img = grp[0][3]
-        with torch.cuda.device(dev):
+        with _nat.on_device(dev):
             rc = L.r3dgw_blend_backward(P, st.R, tot, ctypes.byref(st.cam), st.geom.data_ptr(), st.binning.data_ptr(),
                                         img.data_ptr(), feats.data_ptr(), bgc.data_ptr(), g.data_ptr(),
                                         d_mean2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr(), None, _stream())
@@ -551,7 +551,7 @@ class GaussianRasterizer(nn.Module):
             view, proj = _f32c(s.viewmatrix, dev), _f32c(s.projmatrix, dev)
             present = torch.zeros(P, dtype=torch.bool, device=dev)
             if P:
-                with torch.cuda.device(dev):
+                with _nat.on_device(dev):
                     rc = _nat.lib().r3dgw_mark_visible(P, pos.data_ptr(), view.data_ptr(), proj.data_ptr(),
                                                        present.data_ptr(), _stream())
                 _nat.check(rc, "r3dgw_mark_visible")

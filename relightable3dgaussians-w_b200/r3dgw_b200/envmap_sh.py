@@ -21,7 +21,7 @@ MAX_L = 4
 
 
 def _stream():
-    return torch.cuda.current_stream().cuda_stream
+    return _nat.raw_stream()
 
 
 def _device(device=None):
@@ -66,7 +66,7 @@ def get_coefficients_from_image_device(ibl, l_max=2, resize_width=None, filder_a
     if boost is not None and u8 is None:
         raise ValueError("boost=(scale_high, threshold) applies to uint8 images only")
     bo, scale, thr = (1, float(boost[0]), float(boost[1])) if boost is not None else (0, 1.0, 0.0)
-    with torch.cuda.device(dev):
+    with _nat.on_device(dev):
         size = _target_size(W, resize_width)
         if size is not None:
             Wd, Hd = size
@@ -122,7 +122,7 @@ def sh_rotate_sweep(coeffs, angles_ypr, first_ypr=None, *, out_dtype=torch.float
     o32, o64 = (out.data_ptr(), None) if out_dtype == torch.float32 else (None, out.data_ptr())
     if out_dtype not in (torch.float32, torch.float64):
         raise ValueError("out_dtype must be float32 or float64")
-    with torch.cuda.device(dev):
+    with _nat.on_device(dev):
         rc = _nat.lib().r3dgw_sh_rotate_sweep(l_max, C, F.data_ptr(), None if first is None else first.data_ptr(), B,
                                               A.data_ptr(), o32, o64, _stream())
     _nat.check(rc, "r3dgw_sh_rotate_sweep")

@@ -48,7 +48,7 @@ def _mask_args(mask, C, H, W):
 
 
 def _stream():
-    return torch.cuda.current_stream().cuda_stream
+    return _nat.raw_stream()
 
 
 class _SsimL1Fn(torch.autograd.Function):
@@ -67,7 +67,7 @@ class _SsimL1Fn(torch.autograd.Function):
         dmap = torch.empty(3, C, H, W, dtype=torch.float32, device=x.device) if need_grad else None
         ws = torch.empty(L.r3dgw_image_loss_workspace_bytes(C, H, W), dtype=torch.uint8, device=x.device)
         out = torch.empty(4, dtype=torch.float32, device=x.device)
-        with torch.cuda.device(x.device):
+        with _nat.on_device(x.device):
             rc = L.r3dgw_ssim_l1_forward(C, H, W, x.data_ptr(), y.data_ptr(), mptr, mstride,
                                          None if dmap is None else dmap.data_ptr(), ws.data_ptr(), out.data_ptr(),
                                          _stream())
@@ -82,7 +82,7 @@ class _SsimL1Fn(torch.autograd.Function):
         C, H, W = (int(s) for s in x.shape)
         coef = torch.stack([g_ssim.reshape(()).float(), g_l1.reshape(()).float()]).contiguous()
         grad = torch.empty_like(x)
-        with torch.cuda.device(x.device):
+        with _nat.on_device(x.device):
             rc = _nat.lib().r3dgw_ssim_l1_backward(C, H, W, x.data_ptr(), y.data_ptr(), mptr, mstride, dmap.data_ptr(),
                                                    out.data_ptr(), coef.data_ptr(), grad.data_ptr(), _stream())
         _nat.check(rc, "r3dgw_ssim_l1_backward")
@@ -101,7 +101,7 @@ class _MaskedL1Fn(torch.autograd.Function):
         L = _nat.lib()
         ws = torch.empty(L.r3dgw_image_loss_workspace_bytes(C, H, W), dtype=torch.uint8, device=x.device)
         out = torch.empty(4, dtype=torch.float32, device=x.device)
-        with torch.cuda.device(x.device):
+        with _nat.on_device(x.device):
             rc = L.r3dgw_masked_l1_forward(C, H, W, x.data_ptr(), None if t is None else t.data_ptr(), mptr, mstride,
                                            int(bool(complement)), ws.data_ptr(), out.data_ptr(), _stream())
         _nat.check(rc, "r3dgw_masked_l1_forward")
@@ -114,7 +114,7 @@ class _MaskedL1Fn(torch.autograd.Function):
         x, t, mk, mptr, mstride, out, complement, (C, H, W) = ctx.keep
         coef = g.reshape(1).float().contiguous()
         grad = torch.empty_like(x)
-        with torch.cuda.device(x.device):
+        with _nat.on_device(x.device):
             rc = _nat.lib().r3dgw_masked_l1_backward(C, H, W, x.data_ptr(), None if t is None else t.data_ptr(), mptr,
                                                      mstride, complement, out.data_ptr(), coef.data_ptr(),
                                                      grad.data_ptr(), _stream())
@@ -185,7 +185,7 @@ class _DepthToNormalFn(torch.autograd.Function):
         d = _f32c(depth).reshape(depth.shape[-2], depth.shape[-1])
         H, W = (int(s) for s in d.shape)
         out = torch.empty(H, W, 3, dtype=torch.float32, device=d.device)
-        with torch.cuda.device(d.device):
+        with _nat.on_device(d.device):
             rc = _nat.lib().r3dgw_depth_to_normal_forward(H, W, d.data_ptr(), rays.data_ptr(), out.data_ptr(), _stream())
         _nat.check(rc, "r3dgw_depth_to_normal_forward")
         ctx.keep = (d, rays)
@@ -198,7 +198,7 @@ class _DepthToNormalFn(torch.autograd.Function):
         H, W = (int(s) for s in d.shape)
         g = _f32c(g)
         grad = torch.empty_like(d)
-        with torch.cuda.device(d.device):
+        with _nat.on_device(d.device):
             rc = _nat.lib().r3dgw_depth_to_normal_backward(H, W, d.data_ptr(), rays.data_ptr(), g.data_ptr(),
                                                            grad.data_ptr(), _stream())
         _nat.check(rc, "r3dgw_depth_to_normal_backward")

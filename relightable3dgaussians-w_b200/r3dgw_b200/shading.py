@@ -43,9 +43,9 @@ class _ShadeFn(torch.autograd.Function):
         args = _nat.ShadeArgs(P, int(bool(specular)), int(bool(fix_sky)), int(sh_degree), _ptr(pos), _ptr(nrm), _ptr(alb),
                               _ptr(kr), _ptr(km), _ptr(is_sky), _ptr(fg_index), _ptr(cam), _ptr(env), _ptr(sky), _ptr(lut))
         out = torch.empty(3, P, 3, dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
+        with _nat.on_device(dev):
             rc = _nat.lib().r3dgw_shade_forward(ctypes.byref(args), out[0].data_ptr(), out[1].data_ptr(),
-                                                out[2].data_ptr(), torch.cuda.current_stream().cuda_stream)
+                                                out[2].data_ptr(), _nat.raw_stream())
         _nat.check(rc, "r3dgw_shade_forward")
         ctx.keep = (pos, nrm, alb, kr, km, env, sky, cam, lut, is_sky, fg_index)
         ctx.cfg = (P, int(sh_degree), bool(specular), bool(fix_sky))
@@ -70,10 +70,10 @@ class _ShadeFn(torch.autograd.Function):
         d_km = torch.zeros_like(km) if km is not None else None
         d_env = torch.zeros_like(env)
         d_sky = torch.zeros_like(sky) if sky is not None else None
-        with torch.cuda.device(dev):
+        with _nat.on_device(dev):
             rc = _nat.lib().r3dgw_shade_backward(ctypes.byref(args), _ptr(g_rgb), _ptr(g_dif), _ptr(g_spc), _ptr(d_pos),
                                                  _ptr(d_nrm), _ptr(d_alb), _ptr(d_kr), _ptr(d_km), _ptr(d_env),
-                                                 _ptr(d_sky), torch.cuda.current_stream().cuda_stream)
+                                                 _ptr(d_sky), _nat.raw_stream())
         _nat.check(rc, "r3dgw_shade_backward")
         s = ctx.shapes
         return (d_pos.reshape(s[0]), d_nrm.reshape(s[1]), d_alb.reshape(s[2]),

@@ -20,8 +20,8 @@ def distCUDA2(points: torch.Tensor) -> torch.Tensor:
         return means
     L = _nat.lib()
     ws = torch.empty(L.r3dgw_knn_workspace_bytes(P), dtype=torch.uint8, device=points.device)
-    with torch.cuda.device(points.device):
+    with _nat.on_device(points.device):
         rc = L.r3dgw_knn_dist2(P, pts.data_ptr(), means.data_ptr(), ws.data_ptr(),
-                               torch.cuda.current_stream().cuda_stream)
+                               _nat.raw_stream())
     _nat.check(rc, "r3dgw_knn_dist2")
     return means
