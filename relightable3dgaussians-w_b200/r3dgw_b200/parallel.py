@@ -33,30 +33,40 @@ class GradBucket:
         self.flat = torch.zeros(self.total, dtype=torch.float32, device=self.params[0].device)
 
     def pack(self):
+        """Gradients -> flat bucket: ONE multi-tensor copy (parameters without a gradient contribute zeros)."""
         views = self.flat.split(self.sizes)
+        dst, src = [], []
         for v, p in zip(views, self.params):
             if p.grad is None:
                 v.zero_()
-            else:
-                v.copy_(p.grad.reshape(-1))
+            elif p.grad.data_ptr() != v.data_ptr():      # already a bucket view (gradient accumulated in place)
+                dst.append(v)
+                src.append(p.grad.reshape(-1))
+        if dst:
+            torch._foreach_copy_(dst, src)
         return self.flat
 
     def unpack(self, scale: float = 1.0):
+        """Bucket -> gradients WITHOUT a copy: every p.grad becomes a view of the flat bucket (as DDP's
+        gradient_as_bucket_view), valid until the next pack(); the scale is one in-place kernel over the bucket."""
+        if scale != 1.0:
+            self.flat.mul_(scale)
         for v, p in zip(self.flat.split(self.sizes), self.params):
-            g = v.view_as(p)
-            if scale != 1.0:
-                g = g * scale
-            if p.grad is None:
-                p.grad = g.clone()
-            else:
-                p.grad.copy_(g)
+            p.grad = v.view_as(p)
 
     def all_reduce(self, average_over: int = 0):
+        """pack -> ONE all-reduce -> unpack.  With NCCL and average_over == world size the division rides inside the
+        collective (ReduceOp.AVG): per step 1 multi-tensor copy + 1 collective, no per-parameter kernels."""
         import torch.distributed as dist
         self.pack()
+        scale = 1.0 / average_over if average_over else 1.0
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
-        self.unpack(1.0 / average_over if average_over else 1.0)
+            if average_over == dist.get_world_size() and dist.get_backend() == "nccl":
+                dist.all_reduce(self.flat, op=dist.ReduceOp.AVG)
+                scale = 1.0
+            else:
+                dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+        self.unpack(scale)
 
 
 def sync_densification_stats(xyz_gradient_accum: torch.Tensor, denom: torch.Tensor, max_radii2D: torch.Tensor):
