@@ -372,6 +372,33 @@ constexpr int BWD_WARPS = TILE_PIX / 32;
 #endif
 constexpr bool BWD_DIRECT = R3DGW_BWD_DIRECT_RED != 0;
 
+// Backward-only transcendental shortcuts (R3DGW_BWD_FAST_MATH=0 restores expf / __fdividef).  The forward pass keeps
+// the reference's expf so that every blend decision and n_contrib stay bit-exact; in the backward pass G = exp(power)
+// and 1 / (1 - alpha) only scale gradients (tolerance 1e-3): ex2.approx(power * log2 e) is within ~3 ulp for
+// power in [-5.6, 0] (2 instructions instead of expf's 10), and 1 - alpha lies in [0.01, 1], so the bare MUFU.RCP
+// needs none of __fdividef's range scaling (2 instead of 6).  A pair whose alpha sits within 3 ulp of the 1/255
+// threshold may be classified differently from the forward pass (~20 of 2.4e8 pairs per 1080p frame), which perturbs
+// that one pixel's transmittance by at most 0.4 % for the rest of its walk.
+#ifndef R3DGW_BWD_FAST_MATH
+#define R3DGW_BWD_FAST_MATH 1
+#endif
+__device__ __forceinline__ float bwd_exp(float x) {
+#if R3DGW_BWD_FAST_MATH
+    return __expf(x);
+#else
+    return exp(x);
+#endif
+}
+__device__ __forceinline__ float bwd_rcp(float x) {
+#if R3DGW_BWD_FAST_MATH
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#else
+    return __fdividef(1.f, x);
+#endif
+}
+
 // COLOR = false: the geometry-only pass of the deferred drop-in backward (dL/dfeatures already produced per call by
 // blend_backward_color_cached_kernel): 6 reduced values per (warp, splat) instead of 6 + C
 // QROWS > 0: the six geometry sums of a (warp, splat) pair are not reduced with a shuffle butterfly per splat.  All six
@@ -579,7 +606,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                     bool valid = (k < last_contributor) && !(power > 0.0f) && !(power < b.z);
                     float G = 0.f, alpha = 0.f;
                     if (valid) {
-                        G = exp(power);
+                        G = bwd_exp(power);
                         alpha = min(0.99f, b.y * G);
                         valid = !(alpha < 1.0f / 255.0f);
                     }
@@ -591,7 +618,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
                         if (valid) {
                             // 1/(1-alpha) once (alpha <= 0.99): the reference divides twice; the 2-ulp reciprocal is far
                             // inside the gradient tolerance and the reference's own atomic-order noise
-                            const float inv_1ma = __fdividef(1.f, 1.f - alpha);
+                            const float inv_1ma = bwd_rcp(1.f - alpha);
                             T = T * inv_1ma;
                             const float dchannel_dcolor = alpha * T;
                             // per-channel recurrences on packed FP32 pairs (FFMA2 / FMUL2)
