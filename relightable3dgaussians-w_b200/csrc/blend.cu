@@ -372,25 +372,28 @@ constexpr int BWD_WARPS = TILE_PIX / 32;
 #endif
 constexpr bool BWD_DIRECT = R3DGW_BWD_DIRECT_RED != 0;
 
-// Backward-only transcendental shortcuts (R3DGW_BWD_FAST_MATH=0 restores expf / __fdividef).  The forward pass keeps
-// the reference's expf so that every blend decision and n_contrib stay bit-exact; in the backward pass G = exp(power)
-// and 1 / (1 - alpha) only scale gradients (tolerance 1e-3): ex2.approx(power * log2 e) is within ~3 ulp for
-// power in [-5.6, 0] (2 instructions instead of expf's 10), and 1 - alpha lies in [0.01, 1], so the bare MUFU.RCP
-// needs none of __fdividef's range scaling (2 instead of 6).  A pair whose alpha sits within 3 ulp of the 1/255
-// threshold may be classified differently from the forward pass (~20 of 2.4e8 pairs per 1080p frame), which perturbs
-// that one pixel's transmittance by at most 0.4 % for the rest of its walk.
-#ifndef R3DGW_BWD_FAST_MATH
-#define R3DGW_BWD_FAST_MATH 1
+// Backward-only shortcuts.  1 - alpha lies in [0.01, 1], so the bare MUFU.RCP needs none of __fdividef's range scaling
+// (2 instructions instead of 6; no decision depends on it): on.  exp(power) as ex2.approx(power * log2 e) (2
+// instructions instead of expf's 10, ~5 ulp) was measured too - geometry-only pass 1.18 -> 1.12 ms - but is OFF:
+// a pair whose alpha then lands on the other side of the 1/255 threshold than in the forward pass (a few per frame)
+// perturbs that pixel's transmittance by up to 0.4 % for the rest of its walk, and the colour / opacity gradients of
+// some scenes went from the reference's own run-to-run noise (relative L2 5e-7) to 1e-5 - inside the 1e-3 tolerance,
+// but not worth 0.6 % of a step.  The forward pass always uses the reference's expf (bit-exact decisions, n_contrib).
+#ifndef R3DGW_BWD_FAST_EXP
+#define R3DGW_BWD_FAST_EXP 0
+#endif
+#ifndef R3DGW_BWD_FAST_RCP
+#define R3DGW_BWD_FAST_RCP 1
 #endif
 __device__ __forceinline__ float bwd_exp(float x) {
-#if R3DGW_BWD_FAST_MATH
+#if R3DGW_BWD_FAST_EXP
     return __expf(x);
 #else
     return exp(x);
 #endif
 }
 __device__ __forceinline__ float bwd_rcp(float x) {
-#if R3DGW_BWD_FAST_MATH
+#if R3DGW_BWD_FAST_RCP
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;

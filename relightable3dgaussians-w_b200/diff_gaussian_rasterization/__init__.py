@@ -337,7 +337,7 @@ class _BlendFn(torch.autograd.Function):
         cache = st.alpha_cache
         geo_needed = ctx.needs_input_grad[0] or ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
         m2_ok = ctx.means2D_is_ref or not ctx.needs_input_grad[4]
-        if (_DEFER_BWD and cache is not None and not ctx.use_sh and (C <= 4 or C in _BWDC_WIDE) and st.R > 0
+        if (_DEFER_BWD and cache is not None and not ctx.use_sh and (C <= 4 or (_SPLIT_FUSED_BWD and C in _BWDC_WIDE)) and st.R > 0
                 and ((geo_needed and m2_ok) or (not geo_needed and not ctx.needs_input_grad[4]))):
             # gradient rows padded to 16 B: one vector reduction per (warp, Gaussian) instead of C scalar ones
             stride = 4 if (_GRAD_PAD and C <= 4) else C
