@@ -767,6 +767,11 @@ __device__ __forceinline__ void red_add_v4(float* dst, float a, float b, float c
 __device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
     asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
+__device__ __forceinline__ float ldcs_ordered(const float* p) {   // volatile: stays ahead of the volatile stores below
+    float v;
+    asm volatile("ld.global.cs.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void sts_u16(uint32_t addr, uint16_t v) {
     asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"(v) : "memory");
 }
@@ -777,7 +782,7 @@ __device__ __forceinline__ void sts_u16(uint32_t addr, uint16_t v) {
 // prefetched next to its alpha (8 LDS.U16 + 24 PRMT/MOV per group of 8 for the -1 default): lane 0 records the
 // row's position in the survivor list (a register value) and the reducing lane resolves list -> entry -> id once per
 // row.  Same operations on the same values in the same order: bit-identical partial sums.
-template <int C, int DEPTH, int WROWS, bool VEC, bool LEAN>
+template <int C, int DEPTH, int WROWS, bool VEC, int LEAN>
 __global__ void __launch_bounds__(TILE_PIX, C > 4 ? 4 : 6) blend_backward_color_cached_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatB, int W, int H,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
@@ -851,6 +856,7 @@ __global__ void __launch_bounds__(TILE_PIX, C > 4 ? 4 : 6) blend_backward_color_
         my_rows += (size_t)nsurv * 32;
         int pos = 0;   // pending rows of W (warp-uniform)
         // reduce the pending rows over the 32 pixels: lane l owns row l and issues its splat's C atomics
+        int blk_base = 0;   // LEAN == 2: survivor-list index of W row 0
         auto reduce_rows = [&](int n) {
             __syncwarp();
             constexpr int PARTS = 32 / WROWS;          // lanes per row: each sums 32 / PARTS pixels
@@ -880,8 +886,14 @@ __global__ void __launch_bounds__(TILE_PIX, C > 4 ? 4 : 6) blend_backward_color_
 #pragma unroll
                     for (int off = WROWS; off < 32; off <<= 1) o[ch] += __shfl_xor_sync(0xffffffffu, o[ch], off);
             }
-            if (part == 0 && row < n) {
-                const uint32_t j = LEAN ? (uint32_t)list[s.Wj[warp][row]] : (uint32_t)s.Wj[warp][row];
+            bool nz = LEAN != 2;   // LEAN == 2 also parks rows no pixel blended (1.3 % at config B): nothing to add
+            if (LEAN == 2) {
+#pragma unroll
+                for (int ch = 0; ch < C; ++ch) nz |= (o[ch] != 0.f);
+            }
+            if (part == 0 && row < n && nz) {
+                const uint32_t j = LEAN == 2 ? (uint32_t)list[blk_base + row]
+                                 : LEAN == 1 ? (uint32_t)list[s.Wj[warp][row]] : (uint32_t)s.Wj[warp][row];
                 const uint32_t id = __float_as_uint(s.B[buf][j].w);
                 if (VEC) {   // rows of 4 CQ floats (C <= 4: padded to 4; C = 8, 12, 16: dense)
 #pragma unroll
@@ -897,6 +909,49 @@ __global__ void __launch_bounds__(TILE_PIX, C > 4 ? 4 : 6) blend_backward_color_
         };
         const uint32_t w_base = smem_u32(&s.W[warp][0][lane]), wj_base = smem_u32(&s.Wj[warp][0]);
         uint32_t w_addr = w_base;   // LEAN: &s.W[warp][pos][lane] as a running shared address
+        if constexpr (LEAN == 2) {
+            // blocks of WROWS rows at fixed W slots: no per-row vote / counter / list-position store - a row no pixel
+            // blended is parked as zeros like any other - and no bounds predicate on the loads of a full block
+            static_assert(LEAN != 2 || WROWS % DEPTH == 0, "a block is a whole number of load groups");
+            int g0 = 0;
+            for (; g0 + WROWS <= nsurv; g0 += WROWS) {
+                const float* rp = rows + (size_t)g0 * 32;
+#pragma unroll
+                for (int h = 0; h < WROWS / DEPTH; ++h) {
+                    float al[DEPTH];
+#pragma unroll
+                    for (int u = 0; u < DEPTH; ++u) al[u] = ldcs_ordered(rp + (h * DEPTH + u) * 32);
+#pragma unroll
+                    for (int u = 0; u < DEPTH; ++u) {
+                        sts_f32(w_base + (h * DEPTH + u) * 33 * 4, al[u] * T);
+                        T = T * (1 - al[u]);
+                    }
+                }
+                blk_base = g0;
+                reduce_rows(WROWS);
+            }
+            const int rem = nsurv - g0;
+            if (rem > 0) {
+                const float* rp = rows + (size_t)g0 * 32;
+#pragma unroll
+                for (int h = 0; h < WROWS / DEPTH; ++h) {
+                    if (h * DEPTH >= rem) break;
+                    float al[DEPTH];
+#pragma unroll
+                    for (int u = 0; u < DEPTH; ++u) al[u] = (h * DEPTH + u < rem) ? __ldcs(rp + (h * DEPTH + u) * 32) : 0.f;
+#pragma unroll
+                    for (int u = 0; u < DEPTH; ++u) {
+                        if (h * DEPTH + u < rem) {
+                            sts_f32(w_base + (h * DEPTH + u) * 33 * 4, al[u] * T);
+                            T = T * (1 - al[u]);
+                        }
+                    }
+                }
+                blk_base = g0;
+                reduce_rows(rem);
+            }
+            continue;   // next round
+        }
         for (int g0 = 0; g0 < nsurv; g0 += DEPTH) {
             int js[DEPTH];
             float al[DEPTH];
@@ -930,7 +985,7 @@ __global__ void __launch_bounds__(TILE_PIX, C > 4 ? 4 : 6) blend_backward_color_
     }
 }
 
-template <int C, int DEPTH, int WROWS, bool VEC, bool LEAN>
+template <int C, int DEPTH, int WROWS, bool VEC, int LEAN>
 static int launch_backward_color_cached(dim3 grid, const uint2* ranges, const float4* B, int W, int H,
                                         const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
                                         float* dL_dfeatures, cudaStream_t stream) {
@@ -955,12 +1010,13 @@ static int launch_backward_color_cached_depth(dim3 grid, const uint2* ranges, co
     // C > 4 (the fused 16-channel call): 4 CTAs per SM by launch bounds (64 registers) 0.75 -> 0.64 ms at C = 16; 4 loads
     // in flight 0.67 ms, 8 rows per reduce 0.88 ms
     // R3DGW_BWDC_LEAN=0 selects the pre-diet walk (A/B timing only: 0.369 -> 0.333 ms per call at config B)
-    static const bool lean = [] { const char* e = getenv("R3DGW_BWDC_LEAN"); return !(e && e[0] == '0'); }();
-    if (!lean)
-        return vec ? launch_backward_color_cached<C, 8, 16, true, false>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream)
-                   : launch_backward_color_cached<C, 8, 16, false, false>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
-    return vec ? launch_backward_color_cached<C, 8, 16, true, true>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream)
-               : launch_backward_color_cached<C, 8, 16, false, true>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream);
+    static const int lean = [] { const char* e = getenv("R3DGW_BWDC_LEAN"); return e ? atoi(e) : 2; }();
+#define R3DGW_BWDC_GO(L) (vec ? launch_backward_color_cached<C, 8, 16, true, L>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream) \
+                              : launch_backward_color_cached<C, 8, 16, false, L>(grid, ranges, B, W, H, n_contrib, alpha_cache, dL_dpix, dL_dfeatures, stream))
+    if (lean == 0) return R3DGW_BWDC_GO(0);
+    if (lean == 1) return R3DGW_BWDC_GO(1);
+    return R3DGW_BWDC_GO(2);
+#undef R3DGW_BWDC_GO
 }
 
 int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
