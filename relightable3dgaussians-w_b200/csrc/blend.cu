@@ -248,7 +248,7 @@ struct CachedSmem {
     uint64_t bar[2];
 };
 
-template <int C, bool BLOCKED>
+template <int C>
 __global__ void __launch_bounds__(TILE_PIX) blend_forward_cached_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatB, int W, int H,
     const float* __restrict__ features, const float* __restrict__ bg_color, const float* __restrict__ final_T,
@@ -330,34 +330,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_cached_kernel(
         __syncwarp();
         const float* rows = my_rows;      // next unread row of the warp's run
         my_rows += (size_t)nsurv * 32;
-        int g = 0;
-        if constexpr (BLOCKED) {   // full groups: no bounds predicate on the eight row loads
-            for (; g + CACHED_DEPTH <= nsurv; g += CACHED_DEPTH) {
-                int js[CACHED_DEPTH];
-                float al[CACHED_DEPTH];
-                const float* rp = rows + (size_t)g * 32;
-#pragma unroll
-                for (int u = 0; u < CACHED_DEPTH; ++u) al[u] = ldcs_ordered(rp + u * 32);
-#pragma unroll
-                for (int u = 0; u < CACHED_DEPTH; ++u) js[u] = (int)list[g + u];
-#pragma unroll
-                for (int u = 0; u < CACHED_DEPTH; ++u) {
-                    if (al[u] > 0.f) {
-                        const float alpha = al[u];
-                        const float w = alpha * T;
-                        const float2 w2 = make_float2(w, w);
-#pragma unroll
-                        for (int q = 0; q < CP / 4; ++q) {
-                            const float4 f = s.feat[buf][js[u] * (CP / 4) + q];
-                            Cacc[2 * q] = __ffma2_rn(make_float2(f.x, f.y), w2, Cacc[2 * q]);
-                            Cacc[2 * q + 1] = __ffma2_rn(make_float2(f.z, f.w), w2, Cacc[2 * q + 1]);
-                        }
-                        T = T * (1 - alpha);
-                    }
-                }
-            }
-        }
-        for (; g < nsurv; g += CACHED_DEPTH) {
+        // (measured: full groups without the bounds predicate on the eight row loads - the blocked walk that pays in the
+        // colour-only backward - make this kernel SLOWER, 0.333 vs 0.234 ms: ptxas then interleaves the loads with the
+        // T chain and the lane no longer has eight rows in flight)
+        for (int g = 0; g < nsurv; g += CACHED_DEPTH) {
             int js[CACHED_DEPTH];
             float al[CACHED_DEPTH];
 #pragma unroll
@@ -1077,17 +1053,11 @@ static int launch_forward(dim3 grid, const uint2* ranges, const float4* A, const
                           float* out_color, float* alpha_cache, int cache_mode, cudaStream_t stream) {
     if (cache_mode == 2) {   // replay cached alphas
         const int smem = (int)sizeof(CachedSmem<C>);
-        static const bool blocked = [] { const char* e = getenv("R3DGW_FWDC_BLOCKED"); return e && e[0] == '1'; }();
-        if (blocked) {
-            R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_forward_cached_kernel<C, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        R3DGW_CUDA_TRY(cudaFuncSetAttribute(blend_forward_cached_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        {
             ProfScope ps(KID_BLEND_FWD_CACHED, stream);
-            blend_forward_cached_kernel<C, true><<<grid, TILE_PIX, smem, stream>>>(ranges, B, W, H, features, bg, final_T, n_contrib,
-                                                                                  alpha_cache, out_color);
-        } else {
-            R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_forward_cached_kernel<C, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            ProfScope ps(KID_BLEND_FWD_CACHED, stream);
-            blend_forward_cached_kernel<C, false><<<grid, TILE_PIX, smem, stream>>>(ranges, B, W, H, features, bg, final_T, n_contrib,
-                                                                                   alpha_cache, out_color);
+            blend_forward_cached_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, B, W, H, features, bg, final_T, n_contrib,
+                                                                            alpha_cache, out_color);
         }
         R3DGW_LAUNCH_CHECK();
         return 0;
