@@ -168,6 +168,8 @@ class Stepper:
         if impl == "native":
             import diff_gaussian_rasterization as dgr
             from r3dgw_b200 import image_ops
+            from r3dgw_b200.regularisers import gaussian_regularisers
+            self.reg = gaussian_regularisers
             self.raster = dgr
             self.shade_fn = R.fused_shade_fn(self.lut, 4)
             self.ops = image_ops
@@ -225,24 +227,22 @@ class Stepper:
         rn = out["normal"] * occl3 * sky3
         rs = out["normal_ref"] * occl3 * sky3
         loss = loss + LAMBDA["normal"] * (1 - (rn * rs).sum(dim=0))[None].mean()
-        # min_scale_loss (loss_utils.py:181-191) and depth_loss_gaussians (:139-147): caller-side torch on [P] arrays
+        # min_scale_loss (utils/loss_utils.py:210-220) and depth_loss_gaussians (:140-148)
+        if self.impl == "native":
+            # one masked fixed-order reduction each way, no boolean-mask gathers / sort / host syncs
+            l_scale, l_depth, _ = self.reg(pc.scales, pc.means3D, out["radii"], pc.sky_index()[0],
+                                           cam.world_view_transform, 0.02)
+            return loss + LAMBDA["scale"] * l_scale + LAMBDA["sky_gauss"] * l_depth
+        # the reference's caller-side torch on [P] arrays
         vis = out["radii"] > 0
         is_sky = pc.is_sky.reshape(-1)
         wvt = cam.world_view_transform
         depth = pc.means3D @ wvt[:3, 2:3] + wvt[3, 2]
-        if self.mode == "fused" and self.impl == "native":
-            # same values without boolean-mask indexing (no device->host sync)
-            fg = (vis & ~is_sky).float()
-            loss = loss + LAMBDA["scale"] * (pc.scales.min(dim=-1)[0] * fg).sum() / fg.sum().clamp_min(1.0)
-            sk = (vis & is_sky).float().unsqueeze(1)
-            avg_sky = (depth * sk).sum() / sk.sum().clamp_min(1.0)
-            avg_non = ((depth * fg.unsqueeze(1)).sum() / fg.sum().clamp_min(1.0)).detach()
-        else:
-            if vis.sum() > 0:
-                sc = pc.scales[vis & ~is_sky]
-                loss = loss + LAMBDA["scale"] * torch.sort(sc, dim=-1)[0][..., 0].mean()
-            avg_sky = torch.mean(depth[is_sky & vis])
-            avg_non = torch.mean(depth[(~is_sky) & vis]).detach()
+        if vis.sum() > 0:
+            sc = pc.scales[vis & ~is_sky]
+            loss = loss + LAMBDA["scale"] * torch.sort(sc, dim=-1)[0][..., 0].mean()
+        avg_sky = torch.mean(depth[is_sky & vis])
+        avg_non = torch.mean(depth[(~is_sky) & vis]).detach()
         return loss + LAMBDA["sky_gauss"] * torch.exp(-0.02 * (avg_sky - avg_non))
 
     def step(self, gt, cam=None, sky2=None, occl1=None, on_loss=None):

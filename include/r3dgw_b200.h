@@ -271,6 +271,55 @@ int r3dgw_shade_backward(const r3dgw_shade_args* a,
                          float* dL_droughness, float* dL_dmetalness,
                          float* dL_denv_sh, float* dL_dsky_sh, void* stream);
 
+/* ---- pre-shading fusion ------------------------------------------------
+ * The per-Gaussian caller graph of render() in front of the shading, fused into the shading kernels:
+ *   GaussianModel.get_normal      scene/gaussian_model.py:115-122 (build_rotation / get_minimum_axis /
+ *                                 flip_align_view, utils/general_utils.py:98-119, 158-170)
+ *   dir_pp_normalized             gaussian_renderer/__init__.py:127-129 (safe_normalize(xyz - campos))
+ *   GaussianModel.get_depth       scene/gaussian_model.py:125-130 (+ .repeat(1,3), render():182-183)
+ *   normal "colour" 0.5 n + 0.5   gaussian_renderer/__init__.py:187-188
+ * shade.normals is ignored (may be NULL): the normal is the column of R(q / |q|) at argmin(scale), flipped
+ * towards the camera.  Outputs (and upstream gradients) are addressed as base[stride * i + c]: five dense
+ * [P,3] arrays (stride 3) for the six-call drop-in pattern, or columns of ONE [P,16] feature matrix
+ * (rgb 0-2, diffuse 3-5, specular 6-8, depth 9-11, normal 12-14, ones 15; stride 16) for the single-pass
+ * r3dgw_blend_forward with C = 16.  depth3 / normal01 / ones / normals may be NULL.  normals: dense [P,3]. */
+typedef struct r3dgw_preshade_args {
+    r3dgw_shade_args shade;
+    const float* scales;      /* f32[P,3] post-activation */
+    const float* rotations;   /* f32[P,4] (r,x,y,z) */
+    const float* viewmatrix;  /* f32[16] world_view_transform as stored (transposed), device */
+} r3dgw_preshade_args;
+int r3dgw_preshade_forward(const r3dgw_preshade_args* a, int out_stride, float* rgb, float* diffuse,
+                           float* specular, float* depth3, float* normal01, float* ones, float* normals,
+                           void* stream);
+/* dL_drotations includes the Jacobian of build_rotation's normalisation; scales receive no gradient (argmin). */
+int r3dgw_preshade_backward(const r3dgw_preshade_args* a, int g_stride, const float* dL_drgb,
+                            const float* dL_ddiffuse, const float* dL_dspecular, const float* dL_ddepth3,
+                            const float* dL_dnormal01, float* dL_dpositions, float* dL_drotations,
+                            float* dL_dalbedo, float* dL_droughness, float* dL_dmetalness,
+                            float* dL_denv_sh, float* dL_dsky_sh, void* stream);
+/* GaussianModel.get_normal alone (cam_pos == NULL: no flip, as get_normal(dir_pp_normalized=None)). */
+int r3dgw_gaussian_normal_forward(int P, const float* scales, const float* rotations, const float* positions,
+                                  const float* cam_pos, float* normals, void* stream);
+int r3dgw_gaussian_normal_backward(int P, const float* scales, const float* rotations, const float* positions,
+                                   const float* cam_pos, const float* dL_dnormals, float* dL_drotations,
+                                   void* stream);
+
+/* ---- per-Gaussian regularisers of the training step ------------------------------
+ *   min_scale_loss        utils/loss_utils.py:210-220 (mean over visible foreground Gaussians of min(scale))
+ *   depth_loss_gaussians  utils/loss_utils.py:140-148 (exp(-gamma (mean depth visible sky - mean depth
+ *                         visible foreground [detached])))
+ * visible = radii > 0.  out: device f32[8] = { scale_loss, depth_loss, count fg, count sky, mean depth sky,
+ * mean depth fg, count visible, 0 }.  Fixed-order reduction (bit-reproducible), no host round trip.
+ * backward: grads = device f32[2] { dL/dscale_loss, dL/ddepth_loss }; both outputs are fully overwritten. */
+size_t r3dgw_gaussian_reg_workspace_bytes(int P);
+int r3dgw_gaussian_regularisers_forward(int P, const int* radii, const uint8_t* is_sky, const float* scales,
+                                        const float* means3D, const float* viewmatrix, float gamma,
+                                        char* workspace, float* out, void* stream);
+int r3dgw_gaussian_regularisers_backward(int P, const int* radii, const uint8_t* is_sky, const float* scales,
+                                         const float* viewmatrix, float gamma, const float* out,
+                                         const float* grads, float* dL_dscales, float* dL_dmeans3D, void* stream);
+
 /* ---- image-space post-ops of the training step ---------------------------------
  * Replace torch graphs in the reference (paths relative to /root/reference):
  *   r3dgw_ssim_l1_forward/backward   <- utils/loss_utils.py:27-36 (l1_loss) + :41-99 (ssim / _ssim, 11x11 Gaussian
@@ -326,6 +375,9 @@ int r3dgw_envmap_resize_cubic(int H, int W, int stride, const float* f32, const 
                               float scale, int Hd, int Wd, float* dst /* f32[Hd,Wd,3] */, void* stream);
 int r3dgw_envmap_sh_project(int H, int W, int stride, const float* f32, const uint8_t* u8, int boost, float threshold,
                             float scale, int l_max, char* workspace, double* coeffs, void* stream);
+/* EnvironmentLight.render_sh's sh_render (utils/sh_additional_utils.py:288-299): coeffs f64[(l_max+1)^2,3] ->
+ * out f64[W/2, W, 3], the band-weighted (get_diffuse_coefficients, :267-280) SH reconstruction, linear (no gamma). */
+int r3dgw_envmap_sh_render(int l_max, const double* coeffs, int W, double* out, void* stream);
 int r3dgw_sh_rotate_sweep(int l_max, int C, const double* coeffs, const double* first_ypr, int B,
                           const double* angles_ypr, float* out32, double* out64, void* stream);
 

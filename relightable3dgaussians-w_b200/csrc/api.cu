@@ -28,7 +28,7 @@ const char* const g_prof_names[KID_COUNT] = {
     "blend_forward", "blend_backward", "geometry_backward", "shade_forward", "shade_backward", "knn", "mark_visible",
     "ssim_l1_forward", "ssim_l1_backward", "masked_l1", "depth_to_normal", "blend_forward_cached",
     "blend_backward_geometry", "blend_backward_color_cached", "depth_sort",
-    "envmap_sh_project", "sh_rotate_sweep"};
+    "envmap_sh_project", "sh_rotate_sweep", "gaussian_regularisers"};
 cudaEvent_t prof_event() {
     if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
     cudaEvent_t e; cudaEventCreate(&e); return e;

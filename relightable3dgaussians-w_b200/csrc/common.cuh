@@ -37,7 +37,7 @@ enum KernelId {
     KID_PREPROCESS = 0, KID_DUPLICATE, KID_SORT_HIST, KID_SORT_SCAN, KID_SORT_PASS, KID_RANGES, KID_BLEND_FWD,
     KID_BLEND_BWD, KID_GEOM_BWD, KID_SHADE_FWD, KID_SHADE_BWD, KID_KNN, KID_MARK_VISIBLE, KID_SSIM_FWD, KID_SSIM_BWD,
     KID_MASKED_L1, KID_DEPTH_NORMAL, KID_BLEND_FWD_CACHED, KID_BLEND_BWD_GEOM, KID_BLEND_BWD_COLOR, KID_DEPTH_SORT,
-    KID_ENVMAP_SH, KID_SH_ROTATE, KID_COUNT
+    KID_ENVMAP_SH, KID_SH_ROTATE, KID_GAUSS_REG, KID_COUNT
 };
 extern bool g_profile_on;
 extern int g_sort_prof_kid;   // >= 0: the radix sort's launches are attributed to this kernel id (P-sized depth sort)

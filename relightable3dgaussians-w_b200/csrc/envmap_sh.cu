@@ -174,6 +174,32 @@ envmap_project_finalize_kernel(const double* __restrict__ partial, int H, double
     if (threadIdx.x == 0) coeffs[j] = red[0];
 }
 
+// ---- EnvironmentLight.render_sh: sh_render (utils/sh_additional_utils.py:288-299) ------------------------------------
+// image[y][x][c] = sum_idx Y_idx(theta_y, phi_x) * diffuse_coeff[l(idx)] * coeffs[idx][c], accumulated in index order in
+// FP64 like the numpy loop; theta = y pi / H, phi = x 2 pi / W (get_coefficients_matrix, :159-170).
+struct ShBandScale { double a[SH_MAX_L + 1]; };
+__global__ void __launch_bounds__(128)
+envmap_sh_render_kernel(int l_max, ShNorms norms, ShBandScale band, const double* __restrict__ coeffs, int H, int W,
+                        double* __restrict__ out) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    const double theta = (double)y / ((double)H / M_PI);
+    const double phi = (double)x / ((double)W / (M_PI * 2));
+    const double ct = cos(theta);
+    double acc[3] = {0.0, 0.0, 0.0};
+    for (int l = 0; l <= l_max; ++l)
+        for (int m = -l; m <= l; ++m) {
+            const int i = l * l + l + m, am = m < 0 ? -m : m;
+            double v = norms.k[i] * legendre(l, am, ct);
+            if (m > 0) v = norms.k[i] * cos((double)m * phi) * legendre(l, am, ct);
+            else if (m < 0) v = norms.k[i] * sin((double)am * phi) * legendre(l, am, ct);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) acc[c] += v * (band.a[l] * coeffs[i * 3 + c]);
+        }
+    double* o = out + ((size_t)y * W + x) * 3;
+    o[0] = acc[0]; o[1] = acc[1]; o[2] = acc[2];
+}
+
 // ---- real-SH rotation (Ivanic & Ruedenberg 1996 / errata 1998; what spaudiopy.sph.sh_rotation_matrix computes) ----
 constexpr int ROT_THREADS = 96;                 // >= 81 entries of the l = 4 block
 constexpr int ROT_DOUBLES = 165;                // sum over l = 0..4 of (2l+1)^2
@@ -340,6 +366,37 @@ int r3dgw_envmap_sh_project(int H, int W, int stride, const float* f32, const ui
     }
     R3DGW_LAUNCH_CHECK();
     envmap_project_finalize_kernel<<<n * 3, PROJ_THREADS, 0, stream>>>(partial, H, coeffs);
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_envmap_sh_render(int l_max, const double* coeffs, int W, double* out, void* stream_) {
+    if (l_max < 0 || !coeffs || !out || W < 2) return R3DGW_ERR_BAD_ARG;
+    if (l_max > SH_MAX_L) return R3DGW_ERR_UNSUPPORTED;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int H = W / 2;
+    // get_diffuse_coefficients (utils/sh_additional_utils.py:267-280): pi, 2 pi / 3, then 2 pi (a / b) c for even l, 0 for
+    // odd l, all divided by pi
+    ShBandScale band;
+    for (int l = 0; l <= SH_MAX_L; ++l) {
+        double v;
+        if (l == 0) v = M_PI;
+        else if (l == 1) v = (2 * M_PI) / 3;
+        else if (l % 2 == 0) {
+            const double a = pow(-1.0, l / 2.0 - 1.0), b = (l + 2.0) * (l - 1.0);
+            double fl = 1.0, fh = 1.0;
+            for (int k = 2; k <= l; ++k) fl *= k;
+            for (int k = 2; k <= l / 2; ++k) fh *= k;
+            const double c = fl / (pow(2.0, l) * fh * fh);
+            v = 2 * M_PI * (a / b) * c;
+        } else v = 0.0;
+        band.a[l] = v / M_PI;
+    }
+    dim3 grid((W + 127) / 128, H);
+    {
+        ProfScope ps(KID_ENVMAP_SH, stream);
+        envmap_sh_render_kernel<<<grid, 128, 0, stream>>>(l_max, make_norms(), band, coeffs, H, W, out);
+    }
     R3DGW_LAUNCH_CHECK();
     return 0;
 }

@@ -1,0 +1,146 @@
+// gauss_reg.cu - the per-Gaussian regularisers of the training step as ONE masked fixed-order reduction.
+//
+// Replaces two torch graphs of the reference (boolean-mask gathers, a [P_vis,3] torch.sort, two host syncs):
+//   min_scale_loss        utils/loss_utils.py:210-220   mean over visible foreground Gaussians of their smallest scale
+//   depth_loss_gaussians  utils/loss_utils.py:140-148   exp(-gamma (mean depth of visible sky Gaussians -
+//                                                       mean depth of visible foreground Gaussians [detached]))
+//   (depth = GaussianModel.get_depth, scene/gaussian_model.py:125-130: z of the view-space position)
+// visible = radii > 0 (train.py:77 visibility_filter).  One streaming pass over radii / is_sky / scales / means3D
+// (29 B per Gaussian); per-CTA partial sums are reduced in a fixed order by a one-block finalize kernel, so the two
+// losses are bit-reproducible and nothing returns to the host.
+#include "common.cuh"
+
+namespace r3dgw {
+
+constexpr int REG_THREADS = 256;
+constexpr int REG_MAX_BLOCKS = NUM_SMS * 4;
+constexpr int REG_VALS = 6;       // sum min-scale (fg), count fg, sum depth sky, count sky, sum depth fg, count visible
+
+__device__ __forceinline__ int min_scale_axis(float s0, float s1, float s2) {
+    return (s1 < s0) ? ((s2 < s1) ? 2 : 1) : ((s2 < s0) ? 2 : 0);
+}
+
+__global__ void __launch_bounds__(REG_THREADS)
+gaussian_reg_partial_kernel(int P, const int* __restrict__ radii, const unsigned char* __restrict__ is_sky,
+                            const float* __restrict__ scales, const float* __restrict__ means3D,
+                            const float* __restrict__ vm, double* __restrict__ partial) {
+    float acc[REG_VALS] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const float m2 = vm[2], m6 = vm[6], m10 = vm[10], m14 = vm[14];
+    for (int i = blockIdx.x * REG_THREADS + threadIdx.x; i < P; i += gridDim.x * REG_THREADS) {
+        if (radii[i] <= 0) continue;
+        acc[5] += 1.f;
+        const float depth = m2 * means3D[3 * i] + m6 * means3D[3 * i + 1] + m10 * means3D[3 * i + 2] + m14;
+        if (is_sky && is_sky[i]) {
+            acc[2] += depth; acc[3] += 1.f;
+        } else {
+            acc[0] += fminf(fminf(scales[3 * i], scales[3 * i + 1]), scales[3 * i + 2]);
+            acc[1] += 1.f;
+            acc[4] += depth;
+        }
+    }
+    __shared__ double red[REG_THREADS / 32][REG_VALS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < REG_VALS; ++k) {
+        double a = (double)acc[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (lane == 0) red[warp][k] = a;
+    }
+    __syncthreads();
+    if (threadIdx.x < REG_VALS) {
+        double a = 0.0;
+#pragma unroll
+        for (int w = 0; w < REG_THREADS / 32; ++w) a += red[w][threadIdx.x];
+        partial[(size_t)blockIdx.x * REG_VALS + threadIdx.x] = a;
+    }
+}
+
+// out[8] = { scale_loss, depth_loss, count fg, count sky, mean depth sky, mean depth fg, count visible, 0 }
+__global__ void gaussian_reg_finalize_kernel(int blocks, const double* __restrict__ partial, float gamma,
+                                             float* __restrict__ out) {
+    __shared__ double tot[REG_VALS];
+    if (threadIdx.x < REG_VALS) {
+        double a = 0.0;
+        for (int b = 0; b < blocks; ++b) a += partial[(size_t)b * REG_VALS + threadIdx.x];
+        tot[threadIdx.x] = a;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // torch.mean of an empty selection is NaN (0 / 0); no visible Gaussian at all: the reference returns None
+        // (and train.py then fails) - reported as 0 here
+        const float scale_loss = tot[5] > 0.0 ? (float)(tot[0] / tot[1]) : 0.f;
+        const float avg_sky = (float)(tot[2] / tot[3]);
+        const float avg_fg = (float)(tot[4] / tot[1]);
+        out[0] = scale_loss;
+        out[1] = expf(-gamma * (avg_sky - avg_fg));
+        out[2] = (float)tot[1]; out[3] = (float)tot[3];
+        out[4] = avg_sky; out[5] = avg_fg; out[6] = (float)tot[5]; out[7] = 0.f;
+    }
+}
+
+__global__ void __launch_bounds__(REG_THREADS)
+gaussian_reg_backward_kernel(int P, const int* __restrict__ radii, const unsigned char* __restrict__ is_sky,
+                             const float* __restrict__ scales, const float* __restrict__ vm, float gamma,
+                             const float* __restrict__ out, const float* __restrict__ g,
+                             float* __restrict__ d_scales, float* __restrict__ d_means3D) {
+    const int i = blockIdx.x * REG_THREADS + threadIdx.x;
+    if (i >= P) return;
+    float ds[3] = {0.f, 0.f, 0.f}, dm[3] = {0.f, 0.f, 0.f};
+    if (radii[i] > 0) {
+        if (is_sky && is_sky[i]) {
+            // d exp(-gamma (avg_sky - avg_fg)) / d depth_i = -gamma loss / count_sky  (avg_fg is detached)
+            const float c = g[1] * (-gamma) * out[1] / out[3];
+            dm[0] = c * vm[2]; dm[1] = c * vm[6]; dm[2] = c * vm[10];
+        } else {
+            ds[min_scale_axis(scales[3 * i], scales[3 * i + 1], scales[3 * i + 2])] = g[0] / out[2];
+        }
+    }
+    if (d_scales) { d_scales[3 * i] = ds[0]; d_scales[3 * i + 1] = ds[1]; d_scales[3 * i + 2] = ds[2]; }
+    if (d_means3D) { d_means3D[3 * i] = dm[0]; d_means3D[3 * i + 1] = dm[1]; d_means3D[3 * i + 2] = dm[2]; }
+}
+
+static inline int reg_blocks(int P) { return std::max(1, std::min((P + REG_THREADS - 1) / REG_THREADS, REG_MAX_BLOCKS)); }
+
+}  // namespace r3dgw
+
+using namespace r3dgw;
+
+extern "C" size_t r3dgw_gaussian_reg_workspace_bytes(int P) {
+    return align_up((size_t)reg_blocks(P > 0 ? P : 1) * REG_VALS * sizeof(double), 256);
+}
+
+extern "C" int r3dgw_gaussian_regularisers_forward(int P, const int* radii, const uint8_t* is_sky, const float* scales,
+                                                   const float* means3D, const float* viewmatrix, float gamma,
+                                                   char* workspace, float* out, void* stream_) {
+    if (P < 0 || !workspace || !out || !viewmatrix) return R3DGW_ERR_BAD_ARG;
+    if (P > 0 && (!radii || !scales || !means3D)) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int blocks = reg_blocks(P);
+    {
+        ProfScope ps(KID_GAUSS_REG, stream);
+        gaussian_reg_partial_kernel<<<blocks, REG_THREADS, 0, stream>>>(P, radii, is_sky, scales, means3D, viewmatrix,
+                                                                        reinterpret_cast<double*>(workspace));
+        R3DGW_LAUNCH_CHECK();
+        gaussian_reg_finalize_kernel<<<1, 32, 0, stream>>>(blocks, reinterpret_cast<const double*>(workspace), gamma, out);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int r3dgw_gaussian_regularisers_backward(int P, const int* radii, const uint8_t* is_sky, const float* scales,
+                                                    const float* viewmatrix, float gamma, const float* out,
+                                                    const float* grads, float* dL_dscales, float* dL_dmeans3D,
+                                                    void* stream_) {
+    if (P < 0 || !out || !grads || !viewmatrix) return R3DGW_ERR_BAD_ARG;
+    if (P == 0) return 0;
+    if (!radii || !scales) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    {
+        ProfScope ps(KID_GAUSS_REG, stream);
+        gaussian_reg_backward_kernel<<<(P + REG_THREADS - 1) / REG_THREADS, REG_THREADS, 0, stream>>>(
+            P, radii, is_sky, scales, viewmatrix, gamma, out, grads, dL_dscales, dL_dmeans3D);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}

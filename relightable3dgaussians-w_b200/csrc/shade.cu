@@ -26,7 +26,57 @@ struct ShadeParams {
     const float* positions; const float* normals; const float* albedo; const float* roughness;
     const float* metalness; const unsigned char* is_sky; const int* fg_index; const float* cam_pos;
     const float* env_sh; const float* sky_sh; const float* fg_lut;
+    // pre-shading fusion (GEOM kernels): normals derived in-kernel from scales / rotations, the depth and normal
+    // "colours" of render() produced beside the shaded ones.  Outputs / upstream gradients are addressed with a row
+    // stride so that they are either five dense [P,3] arrays (stride 3) or columns of one [P,16] feature matrix.
+    const float* scales; const float* rotations; const float* viewmatrix;
+    int stride;
 };
+
+// ---- GaussianModel.get_normal (scene/gaussian_model.py:115-122) ---------------------------------------------------
+// build_rotation(q) (utils/general_utils.py:98-119: q / |q|, then the 3x3 from (r,x,y,z)), get_minimum_axis (:158-162:
+// the column of R at argmin(scale)), flip_align_view (:165-170: n *= (n . -viewdir >= 0 ? 1 : -1)).
+struct MinAxisNormal { float3 n; float r, x, y, z, inv_len, sgn; int axis; };
+__device__ __forceinline__ MinAxisNormal min_axis_normal(const float* __restrict__ s3, const float* __restrict__ q4,
+                                                         bool flip, float3 viewdir) {
+    MinAxisNormal m;
+    const float qr = q4[0], qx = q4[1], qy = q4[2], qz = q4[3];
+    const float len = sqrtf(qr * qr + qx * qx + qy * qy + qz * qz);
+    m.inv_len = 1.0f / len;
+    m.r = qr / len; m.x = qx / len; m.y = qy / len; m.z = qz / len;
+    const float s0 = s3[0], s1 = s3[1], s2 = s3[2];
+    m.axis = (s1 < s0) ? ((s2 < s1) ? 2 : 1) : ((s2 < s0) ? 2 : 0);     // first index of the minimum
+    const float r = m.r, x = m.x, y = m.y, z = m.z;
+    if (m.axis == 0) m.n = {1.f - 2.f * (y * y + z * z), 2.f * (x * y + r * z), 2.f * (x * z - r * y)};
+    else if (m.axis == 1) m.n = {2.f * (x * y - r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z + r * x)};
+    else m.n = {2.f * (x * z + r * y), 2.f * (y * z - r * x), 1.f - 2.f * (x * x + y * y)};
+    m.sgn = 1.f;
+    if (flip) {
+        const float d = m.n.x * -viewdir.x + m.n.y * -viewdir.y + m.n.z * -viewdir.z;
+        m.sgn = d >= 0.f ? 1.f : -1.f;
+        m.n = {m.n.x * m.sgn, m.n.y * m.sgn, m.n.z * m.sgn};
+    }
+    return m;
+}
+// cotangent of the (flipped) normal -> cotangent of the un-normalised quaternion the kernel was given
+__device__ __forceinline__ void min_axis_normal_bwd(const MinAxisNormal& m, float3 g, float* gq) {
+    const float g0 = g.x * m.sgn, g1 = g.y * m.sgn, g2 = g.z * m.sgn;
+    const float r = m.r, x = m.x, y = m.y, z = m.z;
+    float hr, hx, hy, hz;     // d / d(normalised quaternion)
+    if (m.axis == 0) {
+        hr = 2.f * (z * g1 - y * g2); hx = 2.f * (y * g1 + z * g2);
+        hy = -4.f * y * g0 + 2.f * (x * g1 - r * g2); hz = -4.f * z * g0 + 2.f * (r * g1 + x * g2);
+    } else if (m.axis == 1) {
+        hr = 2.f * (x * g2 - z * g0); hx = 2.f * y * g0 - 4.f * x * g1 + 2.f * r * g2;
+        hy = 2.f * (x * g0 + z * g2); hz = -2.f * r * g0 - 4.f * z * g1 + 2.f * y * g2;
+    } else {
+        hr = 2.f * (y * g0 - x * g1); hx = 2.f * (z * g0 - r * g1) - 4.f * x * g2;
+        hy = 2.f * (r * g0 + z * g1) - 4.f * y * g2; hz = 2.f * (x * g0 + y * g1);
+    }
+    const float dt = r * hr + x * hx + y * hy + z * hz;
+    gq[0] = (hr - r * dt) * m.inv_len; gq[1] = (hx - x * dt) * m.inv_len;
+    gq[2] = (hy - y * dt) * m.inv_len; gq[3] = (hz - z * dt) * m.inv_len;
+}
 
 __device__ __forceinline__ float gamma_fwd(float x) {
     return powf(fminf(fmaxf(x, 0.0f), 1.0f) + 1e-4f, INV_GAMMA);
@@ -79,9 +129,11 @@ __device__ __forceinline__ LutTap lut_tap(float u, float v) {
 // band index of SH coefficient k (k < 25)
 __device__ __forceinline__ int sh_band(int k) { return k == 0 ? 0 : k < 4 ? 1 : k < 9 ? 2 : k < 16 ? 3 : 4; }
 
-template <int DEG>
+template <int DEG, bool GEOM>
 __global__ void __launch_bounds__(256) shade_forward_kernel(const ShadeParams p, float* __restrict__ rgb,
-                                                            float* __restrict__ diffuse, float* __restrict__ specular) {
+                                                            float* __restrict__ diffuse, float* __restrict__ specular,
+                                                            float* __restrict__ depth3, float* __restrict__ normal01,
+                                                            float* __restrict__ ones, float* __restrict__ normals_out) {
     constexpr int NSH = (DEG + 1) * (DEG + 1);
     __shared__ float s_env[NSH * 3];
     __shared__ float s_sky[12];
@@ -95,6 +147,23 @@ __global__ void __launch_bounds__(256) shade_forward_kernel(const ShadeParams p,
     const float3 pos = {p.positions[3 * i], p.positions[3 * i + 1], p.positions[3 * i + 2]};
     float o_rgb[3], o_dif[3] = {0.f, 0.f, 0.f}, o_spec[3] = {0.f, 0.f, 0.f};
     const bool sky = p.is_sky && p.is_sky[i];
+    float3 n_geom = {0.f, 0.f, 0.f};
+    if (GEOM) {
+        // dir_pp_normalized = safe_normalize(xyz - campos) (gaussian_renderer/__init__.py:127-129), get_normal, and the
+        // depth / normal "colours" (:182-189; get_depth scene/gaussian_model.py:125-130) for EVERY Gaussian, sky included
+        float len;
+        const float3 vd = safe_normalize3({pos.x - s_cam[0], pos.y - s_cam[1], pos.z - s_cam[2]}, len);
+        n_geom = min_axis_normal(p.scales + 3 * i, p.rotations + 4 * i, true, vd).n;
+        const float* vm = p.viewmatrix;
+        const float depth = vm[2] * pos.x + vm[6] * pos.y + vm[10] * pos.z + vm[14];
+        const size_t o = (size_t)p.stride * i;
+        if (depth3) { depth3[o] = depth; depth3[o + 1] = depth; depth3[o + 2] = depth; }
+        if (normal01) {
+            normal01[o] = 0.5f * n_geom.x + 0.5f; normal01[o + 1] = 0.5f * n_geom.y + 0.5f; normal01[o + 2] = 0.5f * n_geom.z + 0.5f;
+        }
+        if (ones) ones[o] = 1.0f;
+        if (normals_out) { normals_out[3 * i] = n_geom.x; normals_out[3 * i + 1] = n_geom.y; normals_out[3 * i + 2] = n_geom.z; }
+    }
     if (sky) {
         if (p.fix_sky) {
             o_rgb[0] = o_rgb[1] = o_rgb[2] = 1.0f;
@@ -111,7 +180,9 @@ __global__ void __launch_bounds__(256) shade_forward_kernel(const ShadeParams p,
         }
     } else {
         const int fi = p.fg_index ? p.fg_index[i] : i;
-        const float3 n = {p.normals[3 * i], p.normals[3 * i + 1], p.normals[3 * i + 2]};
+        float3 n;
+        if (GEOM) n = n_geom;
+        else n = {p.normals[3 * i], p.normals[3 * i + 1], p.normals[3 * i + 2]};
         const float alb[3] = {p.albedo[3 * fi], p.albedo[3 * fi + 1], p.albedo[3 * fi + 2]};
         float w[9];
         irr_coeffs(n.x, n.y, n.z, w);
@@ -160,11 +231,12 @@ __global__ void __launch_bounds__(256) shade_forward_kernel(const ShadeParams p,
             }
         }
     }
+    const size_t so = (size_t)(GEOM ? p.stride : 3) * i;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-        rgb[3 * i + c] = o_rgb[c];
-        if (diffuse) diffuse[3 * i + c] = o_dif[c];
-        if (specular) specular[3 * i + c] = o_spec[c];
+        rgb[so + c] = o_rgb[c];
+        if (diffuse) diffuse[so + c] = o_dif[c];
+        if (specular) specular[so + c] = o_spec[c];
     }
 }
 
@@ -181,10 +253,11 @@ __global__ void __launch_bounds__(256) shade_forward_kernel(const ShadeParams p,
 // Capping at 128 registers for 4 CTAs spills 544 B and is slower, 0.30 ms.)  Warps -> CTA through shared memory, one
 // atomicAdd per coefficient per CTA.
 constexpr int SHADE_BWD_THREADS = 128;
-template <int DEG>
+template <int DEG, bool GEOM>
 __global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
     const ShadeParams p, const float* __restrict__ g_rgb, const float* __restrict__ g_dif,
-    const float* __restrict__ g_spc, float* __restrict__ d_pos, float* __restrict__ d_nrm,
+    const float* __restrict__ g_spc, const float* __restrict__ g_depth3, const float* __restrict__ g_n01,
+    float* __restrict__ d_pos, float* __restrict__ d_nrm, float* __restrict__ d_rot,
     float* __restrict__ d_alb, float* __restrict__ d_kr, float* __restrict__ d_km,
     float* __restrict__ d_env, float* __restrict__ d_sky) {
     constexpr int NSH = (DEG + 1) * (DEG + 1);
@@ -214,9 +287,16 @@ __global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
         float gs[3] = {0.f, 0.f, 0.f}, gi[3] = {0.f, 0.f, 0.f}, gk[3] = {0.f, 0.f, 0.f};
         if (active) {
         const float3 pos = {p.positions[3 * i], p.positions[3 * i + 1], p.positions[3 * i + 2]};
-        const float gr[3] = {g_rgb[3 * i], g_rgb[3 * i + 1], g_rgb[3 * i + 2]};
+        const size_t go = (size_t)(GEOM ? p.stride : 3) * i;
+        const float gr[3] = {g_rgb[go], g_rgb[go + 1], g_rgb[go + 2]};
         float3 gp = {0.f, 0.f, 0.f}, gn = {0.f, 0.f, 0.f};
         const bool sky = p.is_sky && p.is_sky[i];
+        MinAxisNormal mn;
+        if (GEOM) {
+            float len;
+            const float3 vd = safe_normalize3({pos.x - s_cam[0], pos.y - s_cam[1], pos.z - s_cam[2]}, len);
+            mn = min_axis_normal(p.scales + 3 * i, p.rotations + 4 * i, true, vd);
+        }
         if (sky) {
             if (!p.fix_sky) {
                 float len;
@@ -245,9 +325,11 @@ __global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
             }
         } else {
             const int fi = p.fg_index ? p.fg_index[i] : i;
-            const float3 n = {p.normals[3 * i], p.normals[3 * i + 1], p.normals[3 * i + 2]};
+            float3 n;
+            if (GEOM) n = mn.n;
+            else n = {p.normals[3 * i], p.normals[3 * i + 1], p.normals[3 * i + 2]};
             const float alb[3] = {p.albedo[3 * fi], p.albedo[3 * fi + 1], p.albedo[3 * fi + 2]};
-            const float gdv[3] = {g_dif ? g_dif[3 * i] : 0.f, g_dif ? g_dif[3 * i + 1] : 0.f, g_dif ? g_dif[3 * i + 2] : 0.f};
+            const float gdv[3] = {g_dif ? g_dif[go] : 0.f, g_dif ? g_dif[go + 1] : 0.f, g_dif ? g_dif[go + 2] : 0.f};
             float w[9];
             irr_coeffs(n.x, n.y, n.z, w);
             float irr_raw[3], irr[3], D[3];
@@ -266,7 +348,7 @@ __global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
 #pragma unroll
                 for (int c = 0; c < 3; ++c) gD[c] = (gr[c] + gdv[c]) * gamma_bwd(D[c]);
             } else {
-                const float gsv[3] = {g_spc ? g_spc[3 * i] : 0.f, g_spc ? g_spc[3 * i + 1] : 0.f, g_spc ? g_spc[3 * i + 2] : 0.f};
+                const float gsv[3] = {g_spc ? g_spc[go] : 0.f, g_spc ? g_spc[go + 1] : 0.f, g_spc ? g_spc[go + 2] : 0.f};
                 const float kr = p.roughness[fi];
                 const bool has_km = p.metalness != nullptr;
                 const float km = has_km ? p.metalness[fi] : 0.f;
@@ -367,6 +449,20 @@ __global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
             if (d_kr) d_kr[fi] = gkr;
             if (d_km && p.metalness) d_km[fi] = gkm;
         }
+        if (GEOM) {
+            // depth "colour" (3 copies of the view-space z) and normal "colour" (0.5 n + 0.5) of every Gaussian
+            if (g_depth3) {
+                const float gd = g_depth3[go] + g_depth3[go + 1] + g_depth3[go + 2];
+                const float* vm = p.viewmatrix;
+                gp.x += gd * vm[2]; gp.y += gd * vm[6]; gp.z += gd * vm[10];
+            }
+            if (g_n01) { gn.x += 0.5f * g_n01[go]; gn.y += 0.5f * g_n01[go + 1]; gn.z += 0.5f * g_n01[go + 2]; }
+            if (d_rot) {
+                float gq[4];
+                min_axis_normal_bwd(mn, gn, gq);
+                *reinterpret_cast<float4*>(d_rot + 4 * (size_t)i) = make_float4(gq[0], gq[1], gq[2], gq[3]);
+            }
+        }
         if (d_pos) { d_pos[3 * i] = gp.x; d_pos[3 * i + 1] = gp.y; d_pos[3 * i + 2] = gp.z; }
         if (d_nrm) { d_nrm[3 * i] = gn.x; d_nrm[3 * i + 1] = gn.y; d_nrm[3 * i + 2] = gn.z; }
         }   // active
@@ -431,16 +527,79 @@ static ShadeParams to_params(const r3dgw_shade_args* a) {
     p.positions = a->positions; p.normals = a->normals; p.albedo = a->albedo; p.roughness = a->roughness;
     p.metalness = a->metalness; p.is_sky = a->is_sky; p.fg_index = a->fg_index; p.cam_pos = a->cam_pos;
     p.env_sh = a->env_sh; p.sky_sh = a->sky_sh; p.fg_lut = a->fg_lut;
+    p.scales = nullptr; p.rotations = nullptr; p.viewmatrix = nullptr; p.stride = 3;
     return p;
 }
-static int check_args(const r3dgw_shade_args* a) {
+static int check_args(const r3dgw_shade_args* a, bool need_normals = true) {
     if (!a || a->P < 0) return R3DGW_ERR_BAD_ARG;
     if (a->P == 0) return 0;
-    if (!a->positions || !a->normals || !a->albedo || !a->cam_pos || !a->env_sh) return R3DGW_ERR_BAD_ARG;
+    if (!a->positions || (need_normals && !a->normals) || !a->albedo || !a->cam_pos || !a->env_sh) return R3DGW_ERR_BAD_ARG;
     if (a->specular && (!a->roughness || !a->fg_lut)) return R3DGW_ERR_BAD_ARG;
     if (a->is_sky && !a->fix_sky && !a->sky_sh) return R3DGW_ERR_BAD_ARG;
     if (a->sh_degree < 2 || a->sh_degree > 4) return R3DGW_ERR_UNSUPPORTED;
     return 0;
+}
+
+template <bool GEOM>
+static int launch_shade_forward(const ShadeParams& p, float* rgb, float* diffuse, float* specular, float* depth3,
+                                float* normal01, float* ones, float* normals_out, cudaStream_t stream) {
+    const int blocks = (p.P + 255) / 256;
+    ProfScope ps(KID_SHADE_FWD, stream);
+    switch (p.sh_degree) {
+        case 2: shade_forward_kernel<2, GEOM><<<blocks, 256, 0, stream>>>(p, rgb, diffuse, specular, depth3, normal01, ones, normals_out); break;
+        case 3: shade_forward_kernel<3, GEOM><<<blocks, 256, 0, stream>>>(p, rgb, diffuse, specular, depth3, normal01, ones, normals_out); break;
+        default: shade_forward_kernel<4, GEOM><<<blocks, 256, 0, stream>>>(p, rgb, diffuse, specular, depth3, normal01, ones, normals_out); break;
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+template <bool GEOM>
+static int launch_shade_backward(const ShadeParams& p, const float* g_rgb, const float* g_dif, const float* g_spc,
+                                 const float* g_depth3, const float* g_n01, float* d_pos, float* d_nrm, float* d_rot,
+                                 float* d_alb, float* d_kr, float* d_km, float* d_env, float* d_sky, cudaStream_t stream) {
+    const int blocks = std::min((p.P + SHADE_BWD_THREADS - 1) / SHADE_BWD_THREADS, NUM_SMS * 12);
+    ProfScope ps(KID_SHADE_BWD, stream);
+#define R3DGW_SHADE_BWD(D) shade_backward_kernel<D, GEOM><<<blocks, SHADE_BWD_THREADS, 0, stream>>>( \
+        p, g_rgb, g_dif, g_spc, g_depth3, g_n01, d_pos, d_nrm, d_rot, d_alb, d_kr, d_km, d_env, d_sky)
+    switch (p.sh_degree) {
+        case 2: R3DGW_SHADE_BWD(2); break;
+        case 3: R3DGW_SHADE_BWD(3); break;
+        default: R3DGW_SHADE_BWD(4); break;
+    }
+#undef R3DGW_SHADE_BWD
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+__global__ void gaussian_normal_forward_kernel(int P, const float* __restrict__ scales, const float* __restrict__ rotations,
+                                               const float* __restrict__ positions, const float* __restrict__ cam_pos,
+                                               float* __restrict__ normals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    float3 vd = {0.f, 0.f, 0.f};
+    if (cam_pos) {
+        float len;
+        vd = safe_normalize3({positions[3 * i] - cam_pos[0], positions[3 * i + 1] - cam_pos[1], positions[3 * i + 2] - cam_pos[2]}, len);
+    }
+    const MinAxisNormal m = min_axis_normal(scales + 3 * i, rotations + 4 * i, cam_pos != nullptr, vd);
+    normals[3 * i] = m.n.x; normals[3 * i + 1] = m.n.y; normals[3 * i + 2] = m.n.z;
+}
+
+__global__ void gaussian_normal_backward_kernel(int P, const float* __restrict__ scales, const float* __restrict__ rotations,
+                                                const float* __restrict__ positions, const float* __restrict__ cam_pos,
+                                                const float* __restrict__ g_n, float* __restrict__ d_rot) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    float3 vd = {0.f, 0.f, 0.f};
+    if (cam_pos) {
+        float len;
+        vd = safe_normalize3({positions[3 * i] - cam_pos[0], positions[3 * i + 1] - cam_pos[1], positions[3 * i + 2] - cam_pos[2]}, len);
+    }
+    const MinAxisNormal m = min_axis_normal(scales + 3 * i, rotations + 4 * i, cam_pos != nullptr, vd);
+    float gq[4];
+    min_axis_normal_bwd(m, {g_n[3 * i], g_n[3 * i + 1], g_n[3 * i + 2]}, gq);
+    *reinterpret_cast<float4*>(d_rot + 4 * (size_t)i) = make_float4(gq[0], gq[1], gq[2], gq[3]);
 }
 
 }  // namespace r3dgw
@@ -452,17 +611,8 @@ extern "C" int r3dgw_shade_forward(const r3dgw_shade_args* a, float* rgb, float*
     if (rc) return rc;
     if (a->P == 0) return 0;
     if (!rgb) return R3DGW_ERR_BAD_ARG;
-    cudaStream_t stream = (cudaStream_t)stream_;
-    ShadeParams p = to_params(a);
-    const int blocks = (a->P + 255) / 256;
-    ProfScope ps(KID_SHADE_FWD, stream);
-    switch (a->sh_degree) {
-        case 2: shade_forward_kernel<2><<<blocks, 256, 0, stream>>>(p, rgb, diffuse, specular); break;
-        case 3: shade_forward_kernel<3><<<blocks, 256, 0, stream>>>(p, rgb, diffuse, specular); break;
-        default: shade_forward_kernel<4><<<blocks, 256, 0, stream>>>(p, rgb, diffuse, specular); break;
-    }
-    R3DGW_LAUNCH_CHECK();
-    return 0;
+    return launch_shade_forward<false>(to_params(a), rgb, diffuse, specular, nullptr, nullptr, nullptr, nullptr,
+                                       (cudaStream_t)stream_);
 }
 
 extern "C" int r3dgw_shade_backward(const r3dgw_shade_args* a, const float* dL_drgb, const float* dL_ddiffuse,
@@ -473,15 +623,66 @@ extern "C" int r3dgw_shade_backward(const r3dgw_shade_args* a, const float* dL_d
     if (rc) return rc;
     if (a->P == 0) return 0;
     if (!dL_drgb) return R3DGW_ERR_BAD_ARG;
-    cudaStream_t stream = (cudaStream_t)stream_;
-    ShadeParams p = to_params(a);
-    const int blocks = std::min((a->P + SHADE_BWD_THREADS - 1) / SHADE_BWD_THREADS, NUM_SMS * 12);
-    ProfScope ps(KID_SHADE_BWD, stream);
-    switch (a->sh_degree) {
-        case 2: shade_backward_kernel<2><<<blocks, SHADE_BWD_THREADS, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
-        case 3: shade_backward_kernel<3><<<blocks, SHADE_BWD_THREADS, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
-        default: shade_backward_kernel<4><<<blocks, SHADE_BWD_THREADS, 0, stream>>>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_dpositions, dL_dnormals, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh, dL_dsky_sh); break;
-    }
+    return launch_shade_backward<false>(to_params(a), dL_drgb, dL_ddiffuse, dL_dspecular, nullptr, nullptr, dL_dpositions,
+                                        dL_dnormals, nullptr, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh,
+                                        dL_dsky_sh, (cudaStream_t)stream_);
+}
+
+static int preshade_params(const r3dgw_preshade_args* a, int stride, ShadeParams* p) {
+    if (!a) return R3DGW_ERR_BAD_ARG;
+    int rc = check_args(&a->shade, false);
+    if (rc) return rc;
+    if (a->shade.P > 0 && (!a->scales || !a->rotations || !a->viewmatrix || stride < 3)) return R3DGW_ERR_BAD_ARG;
+    *p = to_params(&a->shade);
+    p->scales = a->scales; p->rotations = a->rotations; p->viewmatrix = a->viewmatrix; p->stride = stride;
+    return 0;
+}
+
+extern "C" int r3dgw_preshade_forward(const r3dgw_preshade_args* a, int out_stride, float* rgb, float* diffuse,
+                                      float* specular, float* depth3, float* normal01, float* ones, float* normals,
+                                      void* stream_) {
+    ShadeParams p;
+    int rc = preshade_params(a, out_stride, &p);
+    if (rc) return rc;
+    if (p.P == 0) return 0;
+    if (!rgb) return R3DGW_ERR_BAD_ARG;
+    return launch_shade_forward<true>(p, rgb, diffuse, specular, depth3, normal01, ones, normals, (cudaStream_t)stream_);
+}
+
+extern "C" int r3dgw_preshade_backward(const r3dgw_preshade_args* a, int g_stride, const float* dL_drgb,
+                                       const float* dL_ddiffuse, const float* dL_dspecular, const float* dL_ddepth3,
+                                       const float* dL_dnormal01, float* dL_dpositions, float* dL_drotations,
+                                       float* dL_dalbedo, float* dL_droughness, float* dL_dmetalness,
+                                       float* dL_denv_sh, float* dL_dsky_sh, void* stream_) {
+    ShadeParams p;
+    int rc = preshade_params(a, g_stride, &p);
+    if (rc) return rc;
+    if (p.P == 0) return 0;
+    if (!dL_drgb) return R3DGW_ERR_BAD_ARG;
+    return launch_shade_backward<true>(p, dL_drgb, dL_ddiffuse, dL_dspecular, dL_ddepth3, dL_dnormal01, dL_dpositions,
+                                       nullptr, dL_drotations, dL_dalbedo, dL_droughness, dL_dmetalness, dL_denv_sh,
+                                       dL_dsky_sh, (cudaStream_t)stream_);
+}
+
+extern "C" int r3dgw_gaussian_normal_forward(int P, const float* scales, const float* rotations, const float* positions,
+                                             const float* cam_pos, float* normals, void* stream_) {
+    if (P < 0) return R3DGW_ERR_BAD_ARG;
+    if (P == 0) return 0;
+    if (!scales || !rotations || !normals || (cam_pos && !positions)) return R3DGW_ERR_BAD_ARG;
+    gaussian_normal_forward_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, scales, rotations, positions,
+                                                                                       cam_pos, normals);
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int r3dgw_gaussian_normal_backward(int P, const float* scales, const float* rotations, const float* positions,
+                                              const float* cam_pos, const float* dL_dnormals, float* dL_drotations,
+                                              void* stream_) {
+    if (P < 0) return R3DGW_ERR_BAD_ARG;
+    if (P == 0) return 0;
+    if (!scales || !rotations || !dL_dnormals || !dL_drotations || (cam_pos && !positions)) return R3DGW_ERR_BAD_ARG;
+    gaussian_normal_backward_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, scales, rotations, positions,
+                                                                                        cam_pos, dL_dnormals, dL_drotations);
     R3DGW_LAUNCH_CHECK();
     return 0;
 }

@@ -99,6 +99,24 @@ def process_environment_map_image(img, scale_high, threshold, *, device=None, as
     return c.cpu().numpy() if as_numpy else c
 
 
+def sh_render_device(coeffs, width=600, *, device=None):
+    """sh_render (utils/sh_additional_utils.py:288-299) on the device: coeffs [(l_max+1)^2, 3] -> CUDA f64
+    [width/2, width, 3], linear."""
+    dev = _device(device if device is not None else (coeffs.device if isinstance(coeffs, torch.Tensor)
+                                                       and coeffs.is_cuda else None))
+    c = _as_f64_device(coeffs, dev)
+    n = int(c.shape[0])
+    l_max = int(math.sqrt(n) - 1)             # sh_l_max_from_terms, :390-391
+    if l_max > MAX_L or c.dim() != 2 or c.shape[1] != 3:
+        raise NotImplementedError("sh_render_device: [(l_max+1)^2, 3] coefficients with l_max <= 4")
+    W = int(width)
+    out = torch.empty(W // 2, W, 3, dtype=torch.float64, device=dev)
+    with _nat.on_device(dev):
+        rc = _nat.lib().r3dgw_envmap_sh_render(l_max, c.data_ptr(), W, out.data_ptr(), _stream())
+    _nat.check(rc, "r3dgw_envmap_sh_render")
+    return out
+
+
 def _as_f64_device(x, dev):
     if isinstance(x, torch.Tensor):
         return x.to(device=dev, dtype=torch.float64).contiguous()

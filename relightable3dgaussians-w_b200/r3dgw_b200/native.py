@@ -13,7 +13,7 @@ PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(PKG_ROOT, "csrc")
 LIB_DIR = os.path.join(PKG_ROOT, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libr3dgw_b200.so")
-SOURCES = ["api.cu", "radix_sort.cu", "blend.cu", "knn.cu", "shade.cu", "image_ops.cu", "envmap_sh.cu"]
+SOURCES = ["api.cu", "radix_sort.cu", "blend.cu", "knn.cu", "shade.cu", "image_ops.cu", "envmap_sh.cu", "gauss_reg.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
@@ -29,7 +29,10 @@ SYMBOLS = [
     "r3dgw_masked_l1_forward", "r3dgw_masked_l1_backward", "r3dgw_depth_to_normal_forward",
     "r3dgw_depth_to_normal_backward", "r3dgw_alpha_cache_bytes", "r3dgw_blend_forward_cached",
     "r3dgw_blend_backward_color_cached", "r3dgw_materialize_sorted_keys", "r3dgw_envmap_sh_workspace_bytes",
-    "r3dgw_envmap_resize_cubic", "r3dgw_envmap_sh_project", "r3dgw_sh_rotate_sweep",
+    "r3dgw_envmap_resize_cubic", "r3dgw_envmap_sh_project", "r3dgw_sh_rotate_sweep", "r3dgw_envmap_sh_render",
+    "r3dgw_preshade_forward", "r3dgw_preshade_backward", "r3dgw_gaussian_normal_forward",
+    "r3dgw_gaussian_normal_backward", "r3dgw_gaussian_reg_workspace_bytes", "r3dgw_gaussian_regularisers_forward",
+    "r3dgw_gaussian_regularisers_backward",
 ]
 
 
@@ -107,6 +110,11 @@ class ShadeArgs(ctypes.Structure):
                 ("sky_sh", ctypes.c_void_p), ("fg_lut", ctypes.c_void_p)]
 
 
+class PreshadeArgs(ctypes.Structure):
+    _fields_ = [("shade", ShadeArgs), ("scales", ctypes.c_void_p), ("rotations", ctypes.c_void_p),
+                ("viewmatrix", ctypes.c_void_p)]
+
+
 _lib = None
 
 
@@ -150,7 +158,17 @@ def lib():
     sa = ctypes.POINTER(ShadeArgs)
     L.r3dgw_shade_forward.argtypes = [sa, vp, vp, vp, vp]
     L.r3dgw_shade_backward.argtypes = [sa] + [vp] * 11
+    pa = ctypes.POINTER(PreshadeArgs)
+    L.r3dgw_preshade_forward.argtypes = [pa, ci] + [vp] * 8
+    L.r3dgw_preshade_backward.argtypes = [pa, ci] + [vp] * 13
+    L.r3dgw_gaussian_normal_forward.argtypes = [ci] + [vp] * 6
+    L.r3dgw_gaussian_normal_backward.argtypes = [ci] + [vp] * 7
     sz = ctypes.c_size_t
+    L.r3dgw_gaussian_reg_workspace_bytes.argtypes = [ci]
+    L.r3dgw_gaussian_reg_workspace_bytes.restype = sz
+    L.r3dgw_gaussian_regularisers_forward.argtypes = [ci, vp, vp, vp, vp, vp, ctypes.c_float, vp, vp, vp]
+    L.r3dgw_gaussian_regularisers_backward.argtypes = [ci, vp, vp, vp, vp, ctypes.c_float, vp, vp, vp, vp, vp]
+    L.r3dgw_envmap_sh_render.argtypes = [ci, vp, ci, vp, vp]
     L.r3dgw_image_loss_workspace_bytes.argtypes = [ci, ci, ci]
     L.r3dgw_image_loss_workspace_bytes.restype = sz
     L.r3dgw_ssim_l1_forward.argtypes = [ci, ci, ci, vp, vp, vp, sz, vp, vp, vp, vp]
@@ -174,7 +192,7 @@ def lib():
         fn = getattr(L, name)
         if name not in ("r3dgw_version", "r3dgw_launch_count", "r3dgw_knn_workspace_bytes", "r3dgw_profile_enable",
                         "r3dgw_profile_kernel_name", "r3dgw_image_loss_workspace_bytes", "r3dgw_alpha_cache_bytes",
-                        "r3dgw_envmap_sh_workspace_bytes"):
+                        "r3dgw_envmap_sh_workspace_bytes", "r3dgw_gaussian_reg_workspace_bytes"):
             fn.restype = ci
     _lib = L
     return L

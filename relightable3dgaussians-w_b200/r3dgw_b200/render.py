@@ -14,7 +14,7 @@ from dataclasses import dataclass
 
 import torch
 
-from .shading import shade_gaussians
+from .shading import preshade_gaussians, shade_gaussians, sky_index_of
 
 
 @dataclass
@@ -29,6 +29,14 @@ class GaussianParams:
     roughness: torch.Tensor    # [Pfg,1]
     metalness: torch.Tensor    # [Pfg,1]
     is_sky: torch.Tensor       # [P] bool
+
+    _sky_index = None
+
+    def sky_index(self):
+        """(is_sky u8, foreground rank) for the fused kernels; constant until the Gaussian set changes."""
+        if self._sky_index is None:
+            self._sky_index = sky_index_of(self.is_sky)
+        return self._sky_index
 
     def leaves(self):
         return [self.means3D, self.opacity, self.scales, self.rotations, self.albedo, self.roughness, self.metalness]
@@ -54,14 +62,28 @@ def gaussian_normals(scales, rotations, dir_pp_normalized):
     return n * torch.where(dotprod >= 0, 1.0, -1.0)
 
 
-def fused_shade_fn(fg_lut, sh_degree=4):
+def fused_shade_fn(fg_lut, sh_degree=4, preshade=True):
+    """Shading callback of the native arm.  With preshade=True the whole per-Gaussian graph in front of the rasterizer
+    (get_normal, dir_pp, get_depth, the depth / normal colours, shading) is ONE kernel; with False only
+    the shading is fused and the rest stays caller-side torch, as in round 1."""
     def fn(pc, normals, env_sh, sky_sh, cam_pos, specular, fix_sky):
         return shade_gaussians(pc.means3D, normals, pc.albedo, pc.roughness, pc.metalness, env_sh, cam_pos, fg_lut,
                                sh_degree, specular=specular, sky_sh=sky_sh, is_sky=pc.is_sky, fix_sky=fix_sky)
+
+    def prepare(camera, pc, env_sh, sky_sh, specular, fix_sky, packed=False):
+        return preshade_gaussians(pc.means3D, pc.scales, pc.rotations, pc.albedo, pc.roughness, pc.metalness, env_sh,
+                                  camera.camera_center, camera.world_view_transform, fg_lut, sh_degree,
+                                  specular=specular, sky_sh=sky_sh, fix_sky=fix_sky, packed=packed,
+                                  sky_index=pc.sky_index())
+    if preshade:
+        fn.fused_prepare = prepare
     return fn
 
 
 def _prepare(camera, pc, env_sh, sky_sh, shade_fn, specular, fix_sky):
+    fused = getattr(shade_fn, "fused_prepare", None)
+    if fused is not None:
+        return fused(camera, pc, env_sh, sky_sh, specular, fix_sky)
     cam_pos = camera.camera_center
     dir_pp = pc.means3D - cam_pos.reshape(1, 3)
     dir_pp_n = dir_pp / torch.sqrt(torch.clamp((dir_pp * dir_pp).sum(-1, keepdim=True), min=1e-20))
@@ -156,8 +178,12 @@ def render_fused(camera, pc, env_sh, sky_sh, bg_color, shade_fn, scaling_modifie
         tanfovx=math.tan(camera.FoVx * 0.5), tanfovy=math.tan(camera.FoVy * 0.5), bg=bg_color,
         scale_modifier=scaling_modifier, viewmatrix=camera.world_view_transform,
         projmatrix=camera.full_proj_transform, sh_degree=-1, campos=camera.camera_center, prefiltered=False)
-    colors, diffuse, spec, depth, normal01 = _prepare(camera, pc, env_sh, sky_sh, shade_fn, specular, fix_sky)
-    feats = torch.cat([colors, diffuse, spec, depth, normal01, torch.ones_like(means3D[:, :1])], dim=1)   # [P,16]
+    fused = getattr(shade_fn, "fused_prepare", None)
+    if fused is not None:
+        feats = fused(camera, pc, env_sh, sky_sh, specular, fix_sky, packed=True)                         # [P,16]
+    else:
+        colors, diffuse, spec, depth, normal01 = _prepare(camera, pc, env_sh, sky_sh, shade_fn, specular, fix_sky)
+        feats = torch.cat([colors, diffuse, spec, depth, normal01, torch.ones_like(means3D[:, :1])], dim=1)
     bg16 = torch.cat([bg_color.reshape(3).repeat(5), torch.zeros(1, device=means3D.device)])
     img, radii = dgr.rasterize_gaussians_features(means3D, screenspace_points, feats, pc.opacity, pc.scales,
                                                   pc.rotations, None, s, bg=bg16)

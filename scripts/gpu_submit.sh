@@ -1,0 +1,9 @@
+#!/bin/bash
+# usage: scripts/gpu_submit.sh <timeout_s> <log> <command...>   - retries while the pod answers busy (exit 3)
+T=$1; LOG=$2; shift 2
+for i in $(seq 1 40); do
+  /usr/local/graft/bin/gpurun --timeout "$T" -- "$@" > "$LOG" 2>&1
+  rc=$?
+  if [ $rc -ne 3 ]; then echo "gpurun rc=$rc" >> "$LOG"; exit $rc; fi
+  sleep 150
+done
