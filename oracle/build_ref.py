@@ -14,6 +14,14 @@ prebuilt files travel to the GPU box):
   oracle/_ref/simple_knn/_C.so                    <- simple-knn: spatial.cu, simple_knn.cu, ext.cpp
                                                      (simple-knn/setup.py:24-28)
 
+  oracle/_ref/py/...                              <- the handful of reference .py files render() and the training
+                                                     loss need (gaussian_renderer/__init__.py, scene/gaussian_model.py,
+                                                     scene/cameras.py, scene/NVDIFFREC/{light,util}.py, utils/*.py) and
+                                                     the split-sum table scene/NVDIFFREC/irrmaps/bsdf_256_256.bin,
+                                                     "installed" unmodified so that GPU tests / the reference bench arm
+                                                     can import the STOCK caller code on the GPU box
+                                                     (oracle/ref_loader.load_ref_python supplies the sys.modules stubs)
+
 We do not run the reference's setup.py/CMake; this is a direct nvcc/g++ recipe.  The two forced
 includes (-include cstdint / cfloat) work around headers missing on gcc 13 (SURVEY.md section 8c);
 no source edits.
@@ -76,6 +84,28 @@ def _build_ext(name, root, sources, extra):
     return so
 
 
+PY_FILES = [
+    "gaussian_renderer/__init__.py", "scene/gaussian_model.py", "scene/cameras.py", "scene/NVDIFFREC/light.py",
+    "scene/NVDIFFREC/util.py", "scene/NVDIFFREC/irrmaps/bsdf_256_256.bin", "utils/general_utils.py",
+    "utils/graphics_utils.py", "utils/sh_utils.py", "utils/loss_utils.py", "utils/sh_additional_utils.py",
+    "utils/spherical_harmonics.py", "utils/camera_utils.py", "utils/system_utils.py", "utils/image_utils.py",
+]
+
+
+def stage_python():
+    """Install the reference's caller-side Python (unmodified) under oracle/_ref/py/ - build output, git-ignored."""
+    dst_root = os.path.join(OUT, "py")
+    for rel in PY_FILES:
+        src = os.path.join(REF, rel)
+        if not os.path.exists(src):
+            continue
+        dst = os.path.join(dst_root, rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        if not os.path.exists(dst) or os.path.getmtime(src) > os.path.getmtime(dst):
+            shutil.copyfile(src, dst)
+    return dst_root
+
+
 def build(force=False):
     """Build both reference extensions; no-op when the sources are absent (GPU box)."""
     if not os.path.isdir(DGR):
@@ -94,6 +124,7 @@ def build(force=False):
         _build_ext("simple_knn", KNN, ["spatial.cu", "simple_knn.cu", "ext.cpp"], [])
         open(os.path.join(OUT, "simple_knn", "__init__.py"), "w").close()
     shutil.rmtree(os.path.join(OUT, "_obj"), ignore_errors=True)
+    stage_python()
     return True
 
 

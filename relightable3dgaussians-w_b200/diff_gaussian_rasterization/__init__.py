@@ -29,7 +29,20 @@ from r3dgw_b200 import native as _nat
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
            "rasterize_gaussians_features", "clear_geometry_cache", "last_geometry_state", "set_alpha_cache",
-           "set_deferred_backward"]
+           "set_deferred_backward", "stats", "reset_stats"]
+
+# what the fast path actually did (tests assert on these; cheap integer bumps)
+_stats = {"geometry_builds": 0, "geometry_hits": 0, "blend_plain": 0, "blend_record": 0, "blend_replay": 0,
+          "backward_color_only": 0, "backward_full": 0, "backward_geometry_only": 0, "alpha_cache_refused": 0}
+
+
+def stats():
+    return dict(_stats)
+
+
+def reset_stats():
+    for k in _stats:
+        _stats[k] = 0
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -312,6 +325,7 @@ class _BlendFn(torch.autograd.Function):
                                               out.data_ptr(), None if cache is None else cache.data_ptr(), mode,
                                               _stream())
         _nat.check(rc, "r3dgw_blend_forward_cached")
+        _stats[("blend_plain", "blend_record", "blend_replay")[mode]] += 1
         if mode == 1:
             _alpha_pool["owner"], st.alpha_img = st, img
         ctx.st, ctx.C, ctx.use_sh = st, C, use_sh
@@ -347,6 +361,7 @@ class _BlendFn(torch.autograd.Function):
                                                          img.data_ptr(), cache.data_ptr(), g.data_ptr(),
                                                          dfeat.data_ptr(), stride, _stream())
             _nat.check(rc, "r3dgw_blend_backward_color_cached")
+            _stats["backward_color_only"] += 1
             if stride != C:
                 dfeat = dfeat[:, :C]
             if geo_needed:
@@ -364,6 +379,7 @@ class _BlendFn(torch.autograd.Function):
                                         dmean2D.data_ptr(), dconic.data_ptr(), dopac.data_ptr(),
                                         dfeat.data_ptr(), _stream())
         _nat.check(rc, "r3dgw_blend_backward")
+        _stats["backward_full"] += 1
         g_means2D = dmean2D.clone() if ctx.needs_input_grad[4] else None
         if ctx.use_sh:
             return dmean2D, dconic, dopac, dfeat, g_means2D, torch.zeros(ctx.feat_shape, device=dev), None, None
@@ -382,8 +398,22 @@ _ALPHA_ROUND = 256 << 20
 _alpha_pool = {"buf": None, "owner": None, "prev_calls": 0}
 
 
+_warned = set()
+
+
+def _warn_once(key, msg):
+    if key not in _warned:
+        _warned.add(key)
+        import warnings
+        warnings.warn(msg, RuntimeWarning, stacklevel=3)
+
+
 def _alpha_pool_get(nbytes, device):
     if nbytes > _ALPHA_CACHE_BYTES:
+        _stats["alpha_cache_refused"] += 1
+        _warn_once("alpha_cache_size", f"diff_gaussian_rasterization: alpha cache needs {nbytes / 2**30:.1f} GiB, above "
+                   f"R3DGW_ALPHA_CACHE_GB={_ALPHA_CACHE_BYTES / 2**30:.0f}; repeated blends over this geometry run the "
+                   "full kernels (raise the limit to enable the replay path)")
         return None
     buf = _alpha_pool["buf"]
     if buf is None or buf.device != device or buf.numel() < nbytes:
@@ -446,6 +476,7 @@ def _deferred_geometry_pass(st, dev):
                                         img.data_ptr(), feats.data_ptr(), bgc.data_ptr(), g.data_ptr(),
                                         d_mean2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr(), None, _stream())
         _nat.check(rc, "r3dgw_blend_backward (geometry-only)")
+        _stats["backward_geometry_only"] += 1
         i = j
     return d_mean2D, d_conic, d_opac
 
@@ -493,7 +524,9 @@ def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, mean
            _tkey(s.viewmatrix), _tkey(s.projmatrix), _tkey(s.campos), int(s.sh_degree), bool(s.prefiltered),
            grad_mode)
     if _CACHE_ENABLED and _cache["key"] == key:
+        _stats["geometry_hits"] += 1
         return _cache["entry"]
+    _stats["geometry_builds"] += 1
     prev = _cache["entry"]
     if prev is not None:
         _alpha_pool["prev_calls"] = prev[0].blend_calls

@@ -69,16 +69,17 @@ def gaussian_regularisers(scales, means3D, radii, is_sky, viewmatrix, gamma=0.02
     return _RegFn.apply(scales, means3D, radii, sky, viewmatrix, gamma)
 
 
-def min_scale_loss(radii, scales, is_sky=None, *, means3D=None, viewmatrix=None):
-    """utils/loss_utils.py:210-220 on tensors (the reference takes the GaussianModel: scales = get_scaling,
-    is_sky = get_is_sky)."""
-    dev = scales.device
-    m3 = means3D if means3D is not None else torch.zeros_like(scales)
-    vm = viewmatrix if viewmatrix is not None else torch.eye(4, device=dev)
-    return gaussian_regularisers(scales, m3, radii, is_sky, vm)[0]
+def min_scale_loss(radii, gaussians):
+    """Drop-in for utils/loss_utils.py:210-220, same signature: `gaussians` is any object with the reference
+    GaussianModel's `get_scaling` [P,3] and `get_is_sky` [P,1] getters."""
+    scales = gaussians.get_scaling
+    vm = torch.eye(4, dtype=torch.float32, device=scales.device)
+    return gaussian_regularisers(scales, torch.zeros_like(scales), radii, gaussians.get_is_sky, vm)[0]
 
 
-def depth_loss_gaussians(means3D, is_sky, viewmatrix, visibility_filter, gamma=0.02, *, scales=None):
-    """utils/loss_utils.py:140-148 on tensors (means3D = get_xyz, viewmatrix = camera.world_view_transform)."""
-    sc = scales if scales is not None else torch.ones_like(means3D)
-    return gaussian_regularisers(sc, means3D, visibility_filter.to(torch.int32), is_sky, viewmatrix, gamma)[1]
+def depth_loss_gaussians(gaussians, camera, visibility_filter, gamma=0.02):
+    """Drop-in for utils/loss_utils.py:140-148, same signature (`gaussians.get_xyz`, `gaussians.get_is_sky`,
+    `camera.world_view_transform`)."""
+    xyz = gaussians.get_xyz
+    return gaussian_regularisers(torch.ones_like(xyz), xyz, visibility_filter.to(torch.int32), gaussians.get_is_sky,
+                                 camera.world_view_transform, gamma)[1]

@@ -82,7 +82,7 @@ def mods(native_lib):
 
 
 @pytest.mark.parametrize("name,kw", [("tiny", {}), ("small", {}), ("small", dict(W=333, H=211, seed_offset=77)),
-                                      ("A", {}), ("small", dict(sigma_px=12.0, seed_offset=5))])
+                                      ("A", {}), ("small", dict(sigma_px=12.0, seed_offset=5)), ("B", {})])
 def test_forward_intermediates_bit_exact(mods, name, kw):
     dgr, ref, rl = mods
     from r3dgw_b200.synthetic import make_scene
@@ -114,7 +114,7 @@ def test_forward_intermediates_bit_exact(mods, name, kw):
 
 
 @pytest.mark.parametrize("name,kw,bgv", [("tiny", {}, 0.0), ("small", {}, 0.0), ("small", dict(seed_offset=3), 0.7),
-                                          ("A", {}, 0.0)])
+                                          ("A", {}, 0.0), ("B", {}, 0.0)])
 def test_forward_backward_vs_reference(mods, name, kw, bgv):
     dgr, ref, rl = mods
     from r3dgw_b200.synthetic import make_scene
@@ -145,12 +145,15 @@ def test_forward_backward_vs_reference(mods, name, kw, bgv):
         _grad_close(a, b, nm, b2)
 
 
-def test_n_contrib_and_final_T(mods):
+@pytest.mark.parametrize("name", ["small", "B"])
+def test_n_contrib_and_final_T(mods, name):
+    """The reference-shaped one-shot C-ABI calls, raw through ctypes: r3dgw_rasterize_forward (n_contrib / final_T
+    bit-equal to the reference's image buffer) and r3dgw_rasterize_backward (same gradients as the autograd path)."""
     dgr, ref, rl = mods
     import ctypes
     from r3dgw_b200 import native
     from r3dgw_b200.synthetic import make_scene
-    sc = make_scene("small").to("cuda")
+    sc = make_scene(name).to("cuda")
     P, H, W = sc.P, sc.camera.image_height, sc.camera.image_width
     R_ref, color_ref, radii_ref, gb, bb, ib = _run_ref(ref, sc, sc.colors)
     rb = rl.parse_ref_buffers(P, R_ref, H, W, gb, bb, ib)
@@ -184,6 +187,30 @@ def test_n_contrib_and_final_T(mods):
     assert torch.equal(n_contrib, rb["n_contrib"])
     assert torch.equal(final_T.view(torch.int32), rb["final_T"].view(torch.int32))
     assert (out - color_ref).abs().max().item() <= IMG_TOL
+
+    # raw backward over the buffers the forward call allocated (reference: Rasterizer::backward, rasterizer.h:59-86)
+    gen = torch.Generator().manual_seed(8)
+    dL = (torch.randn(3, H, W, generator=gen) * 1e-3).cuda()
+    z = lambda *shape: torch.zeros(*shape, device="cuda")   # noqa: E731
+    d_m2, d_con, d_op, d_col, d_m3, d_cov, d_sc, d_rot = z(P, 3), z(P, 4), z(P, 1), z(P, 3), z(P, 3), z(P, 6), z(P, 3), z(P, 4)
+    rc = L.r3dgw_rasterize_backward(P, -1, 0, R.value, sc.bg.data_ptr(), ctypes.byref(cam), sc.means3D.data_ptr(), None,
+                                    sc.colors.data_ptr(), sc.scales.data_ptr(), sc.rotations.data_ptr(), None,
+                                    radii.data_ptr(), bufs["g"].data_ptr(), bufs["b"].data_ptr(), bufs["i"].data_ptr(),
+                                    dL.data_ptr(), d_m2.data_ptr(), d_con.data_ptr(), d_op.data_ptr(), d_col.data_ptr(),
+                                    d_m3.data_ptr(), d_cov.data_ptr(), None, d_sc.data_ptr(), d_rot.data_ptr(),
+                                    torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    leaves = [t.clone().requires_grad_(True) for t in (sc.means3D, sc.colors, sc.opacities, sc.scales, sc.rotations)]
+    m2 = torch.zeros_like(sc.means3D, requires_grad=True)
+    dgr.clear_geometry_cache()
+    img, _ = dgr.GaussianRasterizer(_settings(dgr, sc))(means3D=leaves[0], means2D=m2, opacities=leaves[2],
+                                                          colors_precomp=leaves[1], scales=leaves[3], rotations=leaves[4])
+    img.backward(dL)
+    for nm, raw, auto in (("means3D", d_m3, leaves[0].grad), ("means2D", d_m2, m2.grad), ("colors", d_col, leaves[1].grad),
+                          ("opacities", d_op, leaves[2].grad), ("scales", d_sc, leaves[3].grad),
+                          ("rotations", d_rot, leaves[4].grad)):
+        _grad_close(raw, auto, "raw C-ABI " + nm, [auto])       # same kernels twice: only the atomic order differs
 
 
 def test_six_call_render_pattern_gradient_sum(mods):

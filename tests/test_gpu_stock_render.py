@@ -1,0 +1,186 @@
+"""The reference's UNMODIFIED caller code on top of the drop-ins (north_star: "gaussian_renderer/__init__.py and
+scene/relit3DGW_model.py work unchanged").
+
+oracle/build_ref.py installs the reference's gaussian_renderer/__init__.py, scene/gaussian_model.py,
+scene/NVDIFFREC/light.py, utils/*.py and the split-sum table unmodified under the git-ignored oracle/_ref/py/;
+oracle/stock_caller.py imports them with the sys.modules stubs SURVEY.md 8(c) lists.  render() is then executed
+twice on the same reference GaussianModel: once bound to the reference extension + the reference EnvironmentLight,
+once bound to the drop-in `diff_gaussian_rasterization` + the drop-in EnvironmentLight.  Asserted:
+  * identical dict keys / shapes / dtypes, radii bit-equal, images <= 1e-5 (+ the shading tolerance on colours),
+  * the drop-in ran ONE geometry pass + 5 cache hits, recorded the alpha cache on the 2nd blend of the first frame
+    and from the 1st blend on later frames, and took the deferred (colour-only + one geometry-only) backward,
+  * every parameter gradient and viewspace_points.grad (the sum densification reads) within the gradient bar,
+  * the training loss of train.py:78-112 with the reference's loss functions vs the drop-in ones.
+"""
+import os
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LAM = {"dssim": 0.2, "sky_brdf": 0.5, "normal": 0.05, "scale": 100.0, "sky_gauss": 0.05}
+
+
+def _setup(name="small"):
+    import ref_loader
+    import stock_caller as sc_
+    if not (ref_loader.available() and sc_.available()):
+        pytest.skip("oracle/_ref (reference extension + staged reference Python) not built")
+    import diff_gaussian_rasterization as dgr
+    from r3dgw_b200.synthetic import make_scene
+    ref_dgr = ref_loader.load_ref_dgr()
+    r_ref = sc_.load_stock_renderer(ref_dgr, "stock_renderer_ref")
+    r_new = sc_.load_stock_renderer(dgr, "stock_renderer_dropin")
+    assert r_ref.GaussianRasterizer is ref_dgr.GaussianRasterizer and r_new.GaussianRasterizer is dgr.GaussianRasterizer
+    scene = make_scene(name)
+    return sc_, dgr, r_ref, r_new, scene
+
+
+def _view(sc_, scene, dev, seed=3):
+    cam = scene.camera.to(dev)
+    H, W = cam.image_height, cam.image_width
+    sky = torch.ones(1, H, W, device=dev)
+    sky[:, : H // 5] = 0
+    g = torch.Generator().manual_seed(seed)
+    occl = (torch.rand(1, H, W, generator=g) > 0.05).float().to(dev)
+    gt = torch.rand(3, H, W, generator=g).to(dev)
+    return sc_.make_view(cam, sky, occl, gt)
+
+
+def _close_img(a, b, name, tol):
+    err = (a.detach() - b.detach()).abs().max().item()
+    assert err <= tol, f"{name}: max abs err {err:.3e} > {tol}"
+
+
+def _grad_close(a, b, name, rel=1e-3, floor=1e-5, frac=0.999):
+    a, b = a.double(), b.double()
+    scale = max(b.abs().max().item(), 1e-20)
+    l2 = (a - b).norm().item() / max(b.norm().item(), 1e-20)
+    assert l2 <= 3e-3, f"{name}: relative L2 {l2:.3e}"
+    ok = (a - b).abs() <= rel * b.abs() + floor * scale
+    assert ok.double().mean().item() >= frac, f"{name}: only {ok.double().mean().item():.5f} of entries within bar (L2 {l2:.2e})"
+
+
+def test_stock_render_runs_unchanged_on_the_dropins(native_lib):
+    sc_, dgr, r_ref, r_new, scene = _setup("small")
+    dev = torch.device("cuda")
+    view = _view(sc_, scene, dev)
+    bg = torch.zeros(3, device=dev)
+    sky_sh = scene.sky_sh.to(dev).reshape(1, 4, 3).clone().requires_grad_(True)
+    base = scene.env_sh.to(dev)
+
+    from r3dgw_b200.shading import EnvironmentLight
+    lut = sc_.real_fg_lut(dev)
+    outs, grads, losses = {}, {}, {}
+    for arm in ("ref", "new"):
+        gm = sc_.make_ref_model(scene, dev)
+        env_base = base.clone().requires_grad_(True)
+        sky = sky_sh.detach().clone().requires_grad_(True)
+        if arm == "ref":
+            env = sc_.make_ref_envlight(env_base, 4)
+            renderer = r_ref
+        else:
+            env = EnvironmentLight(env_base, 4, fg_lut=lut)
+            renderer = r_new
+            dgr.set_alpha_cache(True)       # also forgets the blend history of earlier tests in this process
+            dgr.reset_stats()
+        pkg = sc_.stock_render(renderer, view, gm, env, sky, bg, debug=False)
+        if arm == "new":
+            st = dgr.stats()
+            assert st["geometry_builds"] == 1 and st["geometry_hits"] == 5, st
+            assert st["blend_plain"] + st["blend_record"] + st["blend_replay"] == 6, st
+            assert st["blend_record"] == 1 and st["blend_replay"] >= 4, st
+        g = torch.Generator().manual_seed(11)
+        loss = 0.0
+        for k in ("render", "diffuse_color", "specular_color", "depth", "normal", "normal_ref"):
+            loss = loss + (pkg[k] * torch.randn(pkg[k].shape, generator=g).to(dev)).sum() * 1e-3
+        loss.backward()
+        if arm == "new":
+            st = dgr.stats()
+            assert st["backward_color_only"] == 5 and st["backward_geometry_only"] == 1 and st["backward_full"] == 0, st
+        outs[arm] = pkg
+        leaves = sc_.model_leaves(gm) + [env_base, sky]
+        grads[arm] = [None if p.grad is None else p.grad.detach().clone() for p in leaves] + \
+            [pkg["viewspace_points"].grad.detach().clone()]
+
+    a, b = outs["ref"], outs["new"]
+    assert set(a.keys()) == set(b.keys())
+    for k in a:
+        assert a[k].shape == b[k].shape and a[k].dtype == b[k].dtype, k
+    assert torch.equal(a["radii"], b["radii"]) and torch.equal(a["visibility_filter"], b["visibility_filter"])
+    for k in ("depth", "normal", "alpha", "normal_ref"):      # pure rasterizer outputs of identical inputs
+        _close_img(a[k], b[k], k, 2e-5 * max(1.0, a[k].abs().max().item()))
+    for k in ("render", "diffuse_color", "specular_color"):   # + fused shading vs the torch graph (1e-5 relative colours)
+        _close_img(a[k], b[k], k, 3e-5)
+    names = ["xyz", "scaling", "rotation", "opacity", "albedo", "roughness", "metalness", "sky_angles", "env_sh",
+             "sky_sh", "viewspace_points"]
+    for nm, ga, gb in zip(names, grads["ref"], grads["new"]):
+        assert (ga is None) == (gb is None), nm
+        if ga is not None:
+            _grad_close(gb, ga, nm)
+
+
+def test_second_frame_records_on_first_blend_and_loss_matches(native_lib):
+    """Two consecutive training steps through the stock render() + train.py's loss: the second frame records the
+    alpha cache on its first blend (5 replays); the loss with the drop-in loss functions equals the reference's."""
+    sc_, dgr, r_ref, r_new, scene = _setup("small")
+    dev = torch.device("cuda")
+    view = _view(sc_, scene, dev)
+    bg = torch.zeros(3, device=dev)
+    ns = sc_.load_ref_python()
+    from r3dgw_b200 import image_ops, regularisers
+    from r3dgw_b200.shading import EnvironmentLight
+    import types
+    new_fns = types.SimpleNamespace(l1_loss=image_ops.l1_loss, ssim=image_ops.ssim,
+                                    min_scale_loss=regularisers.min_scale_loss,
+                                    depth_loss_gaussians=regularisers.depth_loss_gaussians)
+    lut = sc_.real_fg_lut(dev)
+    vals = {}
+    for arm, renderer, fns in (("ref", r_ref, ns.loss_utils), ("new", r_new, new_fns)):
+        gm = sc_.make_ref_model(scene, dev)
+        env_base = scene.env_sh.to(dev).clone().requires_grad_(True)
+        sky = scene.sky_sh.to(dev).reshape(1, 4, 3).clone().requires_grad_(True)
+        env = sc_.make_ref_envlight(env_base, 4) if arm == "ref" else EnvironmentLight(env_base, 4, fg_lut=lut)
+        dgr.set_alpha_cache(True)
+        for it in range(2):
+            with torch.no_grad():                     # an optimizer-style in-place update between the frames
+                for p in sc_.model_leaves(gm):
+                    p.mul_(1.0)
+                    p.grad = None
+            dgr.reset_stats()
+            pkg = sc_.stock_render(renderer, view, gm, env, sky, bg, debug=False)
+            loss = sc_.train_loss(pkg, view, gm, fns, LAM)
+            loss.backward()
+            if arm == "new":
+                st = dgr.stats()
+                assert st["geometry_builds"] == 1 and st["geometry_hits"] == 5, st
+                if it == 1:
+                    assert st["blend_record"] == 1 and st["blend_replay"] == 5, st
+        vals[arm] = (float(loss), [p.grad.detach().clone() for p in sc_.model_leaves(gm)[:4]])
+    assert abs(vals["ref"][0] - vals["new"][0]) <= 2e-5 * abs(vals["ref"][0]), vals
+    for nm, ga, gb in zip(("xyz", "scaling", "rotation", "opacity"), vals["ref"][1], vals["new"][1]):
+        _grad_close(gb, ga, nm)
+
+
+def test_debug_render_keys_and_images(native_lib):
+    sc_, dgr, r_ref, r_new, scene = _setup("tiny")
+    dev = torch.device("cuda")
+    view = _view(sc_, scene, dev)
+    bg = torch.zeros(3, device=dev)
+    from r3dgw_b200.shading import EnvironmentLight
+    lut = sc_.real_fg_lut(dev)
+    with torch.no_grad():
+        gm = sc_.make_ref_model(scene, dev, requires_grad=False)
+        sky = scene.sky_sh.to(dev).reshape(1, 4, 3)
+        a = sc_.stock_render(r_ref, view, gm, sc_.make_ref_envlight(scene.env_sh.to(dev), 4), sky, bg, debug=True)
+        dgr.clear_geometry_cache()
+        dgr.reset_stats()
+        b = sc_.stock_render(r_new, view, gm, EnvironmentLight(scene.env_sh.to(dev), 4, fg_lut=lut), sky, bg, debug=True)
+    st = dgr.stats()
+    assert st["geometry_builds"] == 1 and st["geometry_hits"] == 9, st       # 10 raster calls in debug mode
+    assert set(a.keys()) == set(b.keys()) and "albedo" in b and "sky_color" in b
+    for k in a:
+        if a[k].dtype == torch.float32 and a[k].dim() == 3:
+            _close_img(a[k], b[k], k, 3e-5 * max(1.0, a[k].abs().max().item()))
