@@ -41,8 +41,13 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--workload", default="B", help="synthetic config name (r3dgw_b200.synthetic.CONFIGS)")
-    ap.add_argument("--mode", default="dropin", choices=["dropin", "fused"],
-                    help="dropin: 6 raster calls through the reference API; fused: one 16-channel pass")
+    ap.add_argument("--mode", default="dropin", choices=["dropin", "fused", "stock"],
+                    help="dropin: 6 raster calls through the reference API (repo's render()); fused: one 16-channel "
+                         "pass; stock: the reference's unmodified render() + train.py loss on the drop-in modules")
+    ap.add_argument("--views", type=int, default=0,
+                    help="BASELINE.json config C: V views per step in TOTAL, sharded over the ranks (rank r renders views "
+                         "r, r+N, ...; gradients accumulate, ONE all-reduce, densification statistics all-reduced): strong "
+                         "scaling.  0 (default): one view per rank per step, weak scaling")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
     return ap.parse_args()
@@ -197,6 +202,10 @@ class Stepper:
             self.ops = RefOps
         self.params = self.pc.leaves() + [self.env_sh, self.sky_sh]
 
+    def raster_inputs(self):
+        pc = self.pc
+        return pc.means3D, pc.opacity, pc.scales, pc.rotations
+
     def forward(self, cam=None, sky_mask=None):
         cam = cam or self.cam
         d2n = self.ops.depth_to_normal if sky_mask is not None else None
@@ -245,13 +254,15 @@ class Stepper:
         avg_non = torch.mean(depth[(~is_sky) & vis]).detach()
         return loss + LAMBDA["sky_gauss"] * torch.exp(-0.02 * (avg_sky - avg_non))
 
-    def step(self, gt, cam=None, sky2=None, occl1=None, on_loss=None):
+    def step(self, gt, cam=None, sky2=None, occl1=None, on_loss=None, first=True):
         # optimizer-style in-place touch of every parameter (x *= 1): bumps the tensors' version counters exactly as
-        # an optimizer step does, so nothing computed for the previous iteration (geometry cache) can be reused
-        with self.torch.no_grad():
-            self.torch._foreach_mul_(self.params, 1.0)
-        for p in self.params:
-            p.grad = None
+        # an optimizer step does, so nothing computed for the previous iteration (geometry cache) can be reused.
+        # first=False: a further view of the same step (gradients accumulate, parameters untouched)
+        if first:
+            with self.torch.no_grad():
+                self.torch._foreach_mul_(self.params, 1.0)
+            for p in self.params:
+                p.grad = None
         sky2 = self.sky2 if sky2 is None else sky2
         occl1 = self.occl1 if occl1 is None else occl1
         out = self.forward(cam, sky2)
@@ -259,10 +270,104 @@ class Stepper:
         if on_loss is not None:
             on_loss(loss)      # e2e: the loss value starts its way to the host before the backward pass is enqueued
         loss.backward()
+        self.last_out = out
         return loss
 
     def flat_grads(self):
         return self.torch.cat([p.grad.reshape(-1) for p in self.params if p.grad is not None])
+
+
+class StockStepper:
+    """One training iteration through the reference's UNMODIFIED caller code (oracle/_ref/py, installed by
+    oracle/build_ref.py): gaussian_renderer.render() on a reference GaussianModel + the loss of train.py:78-112.
+    impl == "reference": reference extension, reference EnvironmentLight (torch graph), reference utils.loss_utils -
+    the stock path, nothing of this repo in it.  impl == "native": the same render() bound to the drop-in
+    diff_gaussian_rasterization, the drop-in EnvironmentLight and the drop-in loss functions (what a user gets by
+    swapping the modules and touching nothing else)."""
+
+    def __init__(self, impl, sc, cam, device):
+        import types
+        import torch
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import stock_caller as sc_
+        self.torch, self.sc_, self.impl, self.cam, self.device = torch, sc_, impl, cam, device
+        self.mode = "stock"
+        self.ns = sc_.load_ref_python()
+        if impl == "reference":
+            import ref_loader
+            self.raster = ref_loader.load_ref_dgr()
+            self.renderer = sc_.load_stock_renderer(self.raster, "stock_renderer_ref")
+            self.fns = self.ns.loss_utils
+        else:
+            import diff_gaussian_rasterization as dgr
+            from r3dgw_b200 import image_ops, regularisers
+            self.raster = dgr
+            self.renderer = sc_.load_stock_renderer(dgr, "stock_renderer_dropin")
+            self.fns = types.SimpleNamespace(l1_loss=image_ops.l1_loss, ssim=image_ops.ssim,
+                                             min_scale_loss=regularisers.min_scale_loss,
+                                             depth_loss_gaussians=regularisers.depth_loss_gaussians)
+        self.gm = sc_.make_ref_model(sc, device)
+        self.env_sh = sc.env_sh.to(device).clone().requires_grad_(True)
+        self.sky_sh = sc.sky_sh.to(device).reshape(1, 4, 3).clone().requires_grad_(True)
+        if impl == "reference":
+            self.env = sc_.make_ref_envlight(self.env_sh, 4)
+        else:
+            from r3dgw_b200.shading import EnvironmentLight
+            self.env = EnvironmentLight(self.env_sh, 4, fg_lut=sc_.real_fg_lut(device))
+        self.bg = torch.zeros(3, device=device)
+        H, W = int(cam.image_height), int(cam.image_width)
+        self.sky2 = torch.ones(H, W, device=device)
+        self.sky2[: H // 5] = 0
+        self.occl1 = torch.ones(1, H, W, device=device)
+        self.params = sc_.model_leaves(self.gm) + [self.env_sh, self.sky_sh]
+
+    def raster_inputs(self):
+        gm = self.gm
+        with self.torch.no_grad():
+            return gm.get_xyz.detach(), gm.get_opacity.detach(), gm.get_scaling.detach(), gm.get_rotation.detach()
+
+    def forward(self, cam=None, sky_mask=None):
+        cam = cam or self.cam
+        sky2 = self.sky2 if sky_mask is None else sky_mask
+        view = self.sc_.make_view(cam, sky2.unsqueeze(0))
+        return self.sc_.stock_render(self.renderer, view, self.gm, self.env, self.sky_sh, self.bg, debug=False)
+
+    def step(self, gt, cam=None, sky2=None, occl1=None, on_loss=None, first=True):
+        torch = self.torch
+        if first:
+            with torch.no_grad():
+                torch._foreach_mul_(self.params, 1.0)
+            for p in self.params:
+                p.grad = None
+        cam = cam or self.cam
+        sky2 = self.sky2 if sky2 is None else sky2
+        occl1 = self.occl1 if occl1 is None else occl1
+        view = self.sc_.make_view(cam, sky2.unsqueeze(0), occl1, gt)
+        self.env.set_base(self.env_sh)
+        pkg = self.sc_.stock_render(self.renderer, view, self.gm, self.env, self.sky_sh, self.bg, debug=False)
+        loss = self.sc_.train_loss(pkg, view, self.gm, self.fns, LAMBDA)
+        if on_loss is not None:
+            on_loss(loss)
+        loss.backward()
+        self.last_out = pkg
+        return loss
+
+
+def make_stepper(impl, mode, sc, cam, device):
+    """reference arm: the stock caller when oracle/_ref/py is installed (else the mirror + oracle restatements, noted
+    in the line); native arm: `stock` = stock caller on the drop-ins, `dropin` / `fused` = the repo's own render()."""
+    stock_ok = False
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import stock_caller
+        stock_ok = stock_caller.available()
+    except Exception:   # noqa: BLE001
+        pass
+    if stock_ok and (impl == "reference" or mode == "stock"):
+        return StockStepper(impl, sc, cam, device)
+    if mode == "stock":
+        raise SystemExit("bench.py --mode stock: oracle/_ref/py is absent (run oracle/build_ref.py in the build container)")
+    return Stepper(impl, mode, sc, cam, device)
 
 
 # ---- timing helpers ---------------------------------------------------------------------------------------
@@ -270,6 +375,8 @@ def l2_flush(torch, buf):
     buf.zero_()          # 512 MiB write > 126 MB L2, outside every timed event pair
 
 
+RANK0_SAMPLES = int(os.environ.get("RANK", "0")) == 0     # clocks are sampled by rank 0 only: 8 processes querying
+# NVML in the same step serialise in the driver (r01: 85-100 ms single-step stalls at N = 8)
 LAST_STEP_MS = []      # per-step device times of the most recent timed_steps() call (diagnostics on stderr)
 
 
@@ -293,7 +400,7 @@ def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None, sampler=None):
         a.record()
         fn()
         b.record()
-        if sampler is not None and len(sampler.samples) < 6 and k % 4 == 1:
+        if sampler is not None and len(sampler.samples) < 6 and k % 4 == 1 and RANK0_SAMPLES:
             sampler.sample()      # GPU still busy with the step just enqueued; outside every event pair
     torch.cuda.synchronize()
     if dist is not None:
@@ -461,7 +568,7 @@ def main():
     sc, cam, gt_cpu = build_workload(args.workload, rank, device)
     cfg = CONFIGS[args.workload]
     W, H, P = cfg["W"], cfg["H"], cfg["P"]
-    st = Stepper(args.impl, args.mode, sc, cam, device)
+    st = make_stepper(args.impl, args.mode, sc, cam, device)
     gt = gt_cpu.to(device)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=device)
 
@@ -472,6 +579,33 @@ def main():
         st.step(gt)
         if bucket is not None:
             bucket.all_reduce(average_over=world)   # gradient exchange (64 B per Gaussian) over NVLink, ONE all-reduce
+
+    if args.views > 0:
+        # config C: V views per step, view-sharded: rank r renders views r, r + world, ...
+        from r3dgw_b200.parallel import sync_densification_stats, views_for_rank
+        from r3dgw_b200.synthetic import arc_cameras
+        V = args.views
+        vcams = [c.to(device) for c in arc_cameras(W, H, V, centroid_z=8.0, step_deg=2.0)]
+        mine = views_for_rank(V, rank, world)
+        vgts = {v: torch.rand(3, H, W, generator=torch.Generator().manual_seed(777 + v)).to(device) for v in mine}
+        if bucket is None:
+            bucket = GradBucket(st.params)
+        dens = {"accum": torch.zeros(P, 1, device=device), "denom": torch.zeros(P, 1, device=device),
+                "max_radii": torch.zeros(P, device=device)}
+
+        def step_resident():   # noqa: F811
+            for j, v in enumerate(mine):
+                st.step(vgts[v], vcams[v], first=(j == 0))
+                out = st.last_out
+                with torch.no_grad():
+                    # add_densification_stats (scene/gaussian_model.py:627-629) + max_radii2D (train.py:130), mask-multiplied
+                    vis = out["radii"] > 0
+                    g2 = out["viewspace_points"].grad
+                    dens["accum"].add_(g2[:, :2].norm(dim=-1, keepdim=True) * vis.unsqueeze(1))
+                    dens["denom"].add_(vis.unsqueeze(1))
+                    torch.maximum(dens["max_radii"], out["radii"] * vis, out=dens["max_radii"])
+            bucket.all_reduce(average_over=V)
+            sync_densification_stats(dens["accum"], dens["denom"], dens["max_radii"])
 
     sampler = ClockSampler(local_rank)
     # setup (not part of W): iterations so that torch's caching allocator has grown its pools (the first ones
@@ -491,6 +625,24 @@ def main():
     gpu_launches = (L.r3dgw_launch_count() - launches0) if L else 0
     ms_per_step = total_ms / args.steps
     value = world * 1e3 / ms_per_step if args.impl == "native" else 1e3 / ms_per_step
+    if args.views > 0:
+        value = 1e3 / ms_per_step          # strong scaling: a step is V views whatever the rank count
+        if rank == 0:
+            print(json.dumps({
+                "metric": "train_steps_per_s_8views_fwd+bwd_1M_gaussians_1080p", "value": value, "unit": "steps/s",
+                "views_per_s": value * args.views, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"C: {P} Gaussians, {W}x{H}, {args.views} views/step sharded over {world} rank(s) "
+                                       f"(rank r renders views r, r+N, ...), gradient accumulation, one all-reduce of the "
+                                       f"parameter gradients (ReduceOp.SUM + 1/V) and of the densification statistics per step",
+                           "mode": args.mode, "l2": "512 MiB flush between timed steps"},
+                "clocks": clocks, "gpu_launches": int(gpu_launches), "impl": args.impl,
+                "step_ms": [round(x, 2) for x in LAST_STEP_MS]}))
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
 
     # ---- e2e: host buffers in, loss out, through the public API ----------------------------------------
     pin = lambda t: t.contiguous().pin_memory()   # noqa: E731
@@ -583,7 +735,9 @@ def main():
                                    f"5 raster bwd + masked L1/SSIM, sky-BRDF, normal (depth_to_normal), scale and sky-depth "
                                    f"regularisers as train.py:74-116 ({args.mode})", "l2": "512 MiB flush between timed steps",
                        "host": "Python cyclic GC collected before and disabled inside every timed region",
-                       "mode": args.mode, "views_per_step": world},
+                       "mode": args.mode, "views_per_step": world,
+                       "caller": ("reference render() + train.py loss, unmodified (oracle/_ref/py)" if isinstance(st, StockStepper)
+                                  else "r3dgw_b200.render (the repo's render() / render_fused(), reference call pattern)")},
             "clocks": clocks, "gpu_launches": int(gpu_launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": 4, "h2d_gbps_measured": round(h2d_gbps, 2),
@@ -595,9 +749,13 @@ def main():
         line["impl"] = "reference"
         line["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                                 "sample": "the reference has no CPU rasterizer: its UNMODIFIED CUDA extension "
-                                          "(oracle/_ref, built from /root/reference for sm_100a) + its torch shading "
-                                          "graph, same B200, same steps; CPU port figure is in the native arm's line"}
-        line["e2e"]["note"] = "same host-buffer protocol as the native arm, through the reference's own extension"
+                                          "(oracle/_ref, built from /root/reference for sm_100a) driven by its own "
+                                          "unmodified render() / GaussianModel / EnvironmentLight / loss_utils, same "
+                                          "B200, same steps; CPU port figure is in the native arm's line"}
+        line["e2e"]["note"] = "same host-buffer protocol as the native arm, through the reference's own code"
+        if not isinstance(st, StockStepper):
+            line["config"]["caller"] = ("oracle/_ref/py absent: the repo's render() mirror + oracle/ restatements of the "
+                                        "reference torch graphs around the reference extension")
 
     # ---- extras: fwd-only frames/s (U3), single raster call fwd / fwd+bwd (U1) ---------------------------
     def frame(new_view=True):
@@ -615,15 +773,15 @@ def main():
                                                 cam.full_proj_transform, -1, cam.camera_center, False)
     col = sc.colors.to(device).requires_grad_(True)
     dL = torch.full((3, H, W), 1e-3, device=device)
-    pc = st.pc
+    u_m3, u_op, u_sc, u_rot = [t.detach().clone().requires_grad_(True) for t in st.raster_inputs()]
 
     def u1(bwd):
         if args.impl == "native":
             st.raster.clear_geometry_cache()
-        m2 = torch.zeros_like(pc.means3D, requires_grad=True)
+        m2 = torch.zeros_like(u_m3, requires_grad=True)
         with torch.set_grad_enabled(bwd):
-            img, _ = st.raster.GaussianRasterizer(s)(means3D=pc.means3D, means2D=m2, opacities=pc.opacity,
-                                                     colors_precomp=col, scales=pc.scales, rotations=pc.rotations)
+            img, _ = st.raster.GaussianRasterizer(s)(means3D=u_m3, means2D=m2, opacities=u_op,
+                                                     colors_precomp=col, scales=u_sc, rotations=u_rot)
         if bwd:
             img.backward(dL)
     n1 = max(5, args.steps // 2)
@@ -644,6 +802,16 @@ def main():
         line["fused_single_pass"] = {"value": world * 1e3 / ms_f, "unit": UNIT, "ms_per_step": ms_f,
                                      "api": "r3dgw_b200.render.render_fused (SURVEY 8f N1/N2), same loss and gradients"}
         del st_f
+        # the reference's UNMODIFIED render() + train.py loss on top of the drop-in modules (module swap, nothing else)
+        try:
+            st_s = make_stepper("native", "stock", sc, cam, device)
+            ms_s = timed_steps(torch, lambda: st_s.step(gt), nfz, 4, flush, None) / nfz
+            line["stock_render_on_dropins"] = {"value": 1e3 / ms_s, "unit": UNIT, "ms_per_step": ms_s, "n_gpus": 1,
+                                               "api": "reference gaussian_renderer.render() + GaussianModel getters, "
+                                                      "drop-in rasterizer / EnvironmentLight / loss functions"}
+            del st_s
+        except (SystemExit, Exception) as e:   # noqa: BLE001
+            line["stock_render_on_dropins"] = {"unavailable": str(e)[:200]}
 
     # ---- per-kernel attribution + roofline of the dominant kernel (native arm) ---------------------------
     if args.impl == "native" and not args.no_profile:

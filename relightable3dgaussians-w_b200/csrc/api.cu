@@ -3,6 +3,7 @@
 // diff-gaussian-rasterization/cuda_rasterizer/rasterizer_impl.cu:198-433.
 #include <algorithm>
 #include <climits>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -417,7 +418,9 @@ int r3dgw_geometry_backward(int P, int D, int M, const r3dgw_camera* cam, const 
     gp.dL_dscale = dL_dscale; gp.dL_drot = dL_drot;
     {
         ProfScope ps(KID_GEOM_BWD, stream);
-        geometry_backward_kernel<<<(P + 255) / 256, 256, 0, stream>>>(gp);
+        static const bool f32_chain = [] { const char* e = getenv("R3DGW_GEOM_BWD_F32"); return e && e[0] == '1'; }();
+        if (f32_chain) geometry_backward_kernel<float><<<(P + 255) / 256, 256, 0, stream>>>(gp);
+        else geometry_backward_kernel<double><<<(P + 255) / 256, 256, 0, stream>>>(gp);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;

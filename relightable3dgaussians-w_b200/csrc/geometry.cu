@@ -514,6 +514,15 @@ struct GeomBackwardParams {
     float* dL_drot;               // [P,4]
 };
 
+// `real` is the type the chain is EVALUATED in.  The reference evaluates it in float (backward.cu:144-396), where the
+// cov2D -> cov3D -> scale / rotation chain cancels heavily ((denom - a c) is -b^2 by subtraction, the quaternion
+// gradient is a sum of differences of O(s^2 dL/dSigma) terms): against an FP64 evaluation of the same formulas
+// (oracle/raster_f64.cu) a float chain is off by 2e-4 (scales) / 9e-4 (rotations) relative L2 at config B - the
+// reference's own error is the same size - while the float screen-space gradients pushed through an FP64 chain are
+// off by 6e-6 / 1.4e-5 (scripts/diag_f64_split.py, profiles/r02_grad_f64.txt).  The kernel is HBM-bound (160 B per
+// visible Gaussian, ~600 flops), so real = double is the default: same formulas, same float decisions (clamp flags,
+// radii > 0), float inputs and outputs, FP64 in between.  R3DGW_GEOM_BWD_F32=1 selects the float instantiation.
+template <typename real>
 __global__ void __launch_bounds__(256) geometry_backward_kernel(const GeomBackwardParams p) {
     __shared__ float s_view[16], s_proj[16];
     if (threadIdx.x < 16) {
@@ -529,41 +538,52 @@ __global__ void __launch_bounds__(256) geometry_backward_kernel(const GeomBackwa
     const float3 mean = {p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]};
     const float* cov3D = p.cov3Ds + 6 * (size_t)idx;
     const float4 gconic4 = reinterpret_cast<const float4*>(p.dL_dconic)[idx];
-    const float gcx = gconic4.x, gcy = gconic4.y, gcz = gconic4.w;
+    const real gcx = gconic4.x, gcy = gconic4.y, gcz = gconic4.w;
 
     // ---- recompute the forward projection ----------------------------------------------------
-    float3 t = xform_4x3(mean, view);
-    const float limx = 1.3f * p.tan_fovx, limy = 1.3f * p.tan_fovy;
-    const float txtz = t.x / t.z, tytz = t.y / t.z;
-    t.x = min(limx, max(-limx, txtz)) * t.z;
-    t.y = min(limy, max(-limy, tytz)) * t.z;
-    const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
-    const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
-    const float hx = p.focal_x, hy = p.focal_y;
-    const float j00 = hx / t.z, j02 = -(hx * t.x) / (t.z * t.z);
-    const float j11 = hy / t.z, j12 = -(hy * t.y) / (t.z * t.z);
+    // clamp DECISIONS on the float values the forward pass saw (backward.cu:166-176)
+    const float3 tf = xform_4x3(mean, view);
+    const float limxf = 1.3f * p.tan_fovx, limyf = 1.3f * p.tan_fovy;
+    const float txtzf = tf.x / tf.z, tytzf = tf.y / tf.z;
+    const bool clamp_x = txtzf < -limxf || txtzf > limxf, clamp_y = tytzf < -limyf || tytzf > limyf;
+    const real x_grad_mul = clamp_x ? real(0) : real(1), y_grad_mul = clamp_y ? real(0) : real(1);
+    const real mx = mean.x, my = mean.y, mz = mean.z;
+    real tx = real(view[0]) * mx + real(view[4]) * my + real(view[8]) * mz + real(view[12]);
+    real ty = real(view[1]) * mx + real(view[5]) * my + real(view[9]) * mz + real(view[13]);
+    const real tz_ = real(view[2]) * mx + real(view[6]) * my + real(view[10]) * mz + real(view[14]);
+    if (sizeof(real) == sizeof(float)) {      // the reference's float expression, clamp included
+        tx = real(fminf(limxf, fmaxf(-limxf, txtzf)) * tf.z);
+        ty = real(fminf(limyf, fmaxf(-limyf, tytzf)) * tf.z);
+    } else {
+        if (clamp_x) tx = real(txtzf < -limxf ? -limxf : limxf) * tz_;
+        if (clamp_y) ty = real(tytzf < -limyf ? -limyf : limyf) * tz_;
+    }
+    const real hx = p.focal_x, hy = p.focal_y;
+    const real j00 = hx / tz_, j02 = -(hx * tx) / (tz_ * tz_);
+    const real j11 = hy / tz_, j12 = -(hy * ty) / (tz_ * tz_);
     // u, v: first two columns of T = W * J;  W[k][r] = view[k + 4 r]
-    float u[3], v[3];
+    real u[3], v[3];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-        u[r] = view[0 + 4 * r] * j00 + view[2 + 4 * r] * j02;
-        v[r] = view[1 + 4 * r] * j11 + view[2 + 4 * r] * j12;
+        u[r] = real(view[0 + 4 * r]) * j00 + real(view[2 + 4 * r]) * j02;
+        v[r] = real(view[1 + 4 * r]) * j11 + real(view[2 + 4 * r]) * j12;
     }
-    const float V[3][3] = {{cov3D[0], cov3D[1], cov3D[2]}, {cov3D[1], cov3D[3], cov3D[4]}, {cov3D[2], cov3D[4], cov3D[5]}};
-    float Vu[3], Vv[3];
+    const real V[3][3] = {{real(cov3D[0]), real(cov3D[1]), real(cov3D[2])}, {real(cov3D[1]), real(cov3D[3]), real(cov3D[4])},
+                          {real(cov3D[2]), real(cov3D[4]), real(cov3D[5])}};
+    real Vu[3], Vv[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         Vu[i] = V[i][0] * u[0] + V[i][1] * u[1] + V[i][2] * u[2];
         Vv[i] = V[i][0] * v[0] + V[i][1] * v[1] + V[i][2] * v[2];
     }
-    const float a = (u[0] * Vu[0] + u[1] * Vu[1] + u[2] * Vu[2]) + 0.3f;
-    const float b = u[0] * Vv[0] + u[1] * Vv[1] + u[2] * Vv[2];
-    const float c = (v[0] * Vv[0] + v[1] * Vv[1] + v[2] * Vv[2]) + 0.3f;
+    const real a = (u[0] * Vu[0] + u[1] * Vu[1] + u[2] * Vu[2]) + real(0.3f);
+    const real b = u[0] * Vv[0] + u[1] * Vv[1] + u[2] * Vv[2];
+    const real c = (v[0] * Vv[0] + v[1] * Vv[1] + v[2] * Vv[2]) + real(0.3f);
 
-    const float denom = a * c - b * b;
-    float dL_da = 0, dL_db = 0, dL_dc = 0;
-    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
-    float gcov[6] = {0, 0, 0, 0, 0, 0};
+    const real denom = a * c - b * b;
+    real dL_da = 0, dL_db = 0, dL_dc = 0;
+    const real denom2inv = real(1) / ((denom * denom) + real(0.0000001f));
+    real gcov[6] = {0, 0, 0, 0, 0, 0};
     if (denom2inv != 0) {
         dL_da = denom2inv * (-c * c * gcx + 2 * b * c * gcy + (denom - a * c) * gcz);
         dL_dc = denom2inv * (-a * a * gcz + 2 * a * b * gcy + (denom - a * c) * gcx);
@@ -577,37 +597,38 @@ __global__ void __launch_bounds__(256) geometry_backward_kernel(const GeomBackwa
         gcov[4] = 2 * u[2] * u[1] * dL_da + (u[1] * v[2] + u[2] * v[1]) * dL_db + 2 * v[1] * v[2] * dL_dc;
     }
 #pragma unroll
-    for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = gcov[i];
+    for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = (float)gcov[i];
 
-    float gu[3], gv[3];
+    real gu[3], gv[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         gu[i] = 2 * Vu[i] * dL_da + Vv[i] * dL_db;
         gv[i] = 2 * Vv[i] * dL_dc + Vu[i] * dL_db;
     }
-    const float dL_dJ00 = view[0] * gu[0] + view[4] * gu[1] + view[8] * gu[2];
-    const float dL_dJ02 = view[2] * gu[0] + view[6] * gu[1] + view[10] * gu[2];
-    const float dL_dJ11 = view[1] * gv[0] + view[5] * gv[1] + view[9] * gv[2];
-    const float dL_dJ12 = view[2] * gv[0] + view[6] * gv[1] + view[10] * gv[2];
-    const float tz = 1.f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
-    const float dL_dtx = x_grad_mul * -hx * tz2 * dL_dJ02;
-    const float dL_dty = y_grad_mul * -hy * tz2 * dL_dJ12;
-    const float dL_dtz = -hx * tz2 * dL_dJ00 - hy * tz2 * dL_dJ11 + (2 * hx * t.x) * tz3 * dL_dJ02 + (2 * hy * t.y) * tz3 * dL_dJ12;
-    float3 gmean = {view[0] * dL_dtx + view[1] * dL_dty + view[2] * dL_dtz,
-                    view[4] * dL_dtx + view[5] * dL_dty + view[6] * dL_dtz,
-                    view[8] * dL_dtx + view[9] * dL_dty + view[10] * dL_dtz};
+    const real dL_dJ00 = real(view[0]) * gu[0] + real(view[4]) * gu[1] + real(view[8]) * gu[2];
+    const real dL_dJ02 = real(view[2]) * gu[0] + real(view[6]) * gu[1] + real(view[10]) * gu[2];
+    const real dL_dJ11 = real(view[1]) * gv[0] + real(view[5]) * gv[1] + real(view[9]) * gv[2];
+    const real dL_dJ12 = real(view[2]) * gv[0] + real(view[6]) * gv[1] + real(view[10]) * gv[2];
+    const real tz = real(1) / tz_, tz2 = tz * tz, tz3 = tz2 * tz;
+    const real dL_dtx = x_grad_mul * -hx * tz2 * dL_dJ02;
+    const real dL_dty = y_grad_mul * -hy * tz2 * dL_dJ12;
+    const real dL_dtz = -hx * tz2 * dL_dJ00 - hy * tz2 * dL_dJ11 + (2 * hx * tx) * tz3 * dL_dJ02 + (2 * hy * ty) * tz3 * dL_dJ12;
+    real gmx = real(view[0]) * dL_dtx + real(view[1]) * dL_dty + real(view[2]) * dL_dtz;
+    real gmy = real(view[4]) * dL_dtx + real(view[5]) * dL_dty + real(view[6]) * dL_dtz;
+    real gmz = real(view[8]) * dL_dtx + real(view[9]) * dL_dty + real(view[10]) * dL_dtz;
 
     // ---- screen-space mean gradient through the projection (backward.cu:366-387) --------------
     {
-        float4 m_hom = xform_4x4(mean, proj);
-        float m_w = 1.0f / (m_hom.w + 0.0000001f);
-        float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
-        float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
-        float gx = p.dL_dmean2D[3 * (size_t)idx], gy = p.dL_dmean2D[3 * (size_t)idx + 1];
-        gmean.x += (proj[0] * m_w - proj[3] * mul1) * gx + (proj[1] * m_w - proj[3] * mul2) * gy;
-        gmean.y += (proj[4] * m_w - proj[7] * mul1) * gx + (proj[5] * m_w - proj[7] * mul2) * gy;
-        gmean.z += (proj[8] * m_w - proj[11] * mul1) * gx + (proj[9] * m_w - proj[11] * mul2) * gy;
+        const real hw = real(proj[3]) * mx + real(proj[7]) * my + real(proj[11]) * mz + real(proj[15]);
+        const real m_w = real(1) / (hw + real(0.0000001f));
+        const real mul1 = (real(proj[0]) * mx + real(proj[4]) * my + real(proj[8]) * mz + real(proj[12])) * m_w * m_w;
+        const real mul2 = (real(proj[1]) * mx + real(proj[5]) * my + real(proj[9]) * mz + real(proj[13])) * m_w * m_w;
+        const real gx = p.dL_dmean2D[3 * (size_t)idx], gy = p.dL_dmean2D[3 * (size_t)idx + 1];
+        gmx += (real(proj[0]) * m_w - real(proj[3]) * mul1) * gx + (real(proj[1]) * m_w - real(proj[3]) * mul2) * gy;
+        gmy += (real(proj[4]) * m_w - real(proj[7]) * mul1) * gx + (real(proj[5]) * m_w - real(proj[7]) * mul2) * gy;
+        gmz += (real(proj[8]) * m_w - real(proj[11]) * mul1) * gx + (real(proj[9]) * m_w - real(proj[11]) * mul2) * gy;
     }
+    float3 gmean = {(float)gmx, (float)gmy, (float)gmz};
     if (p.shs != nullptr) {
         float3 g = sh_to_rgb_bwd(idx, p.D, p.M, p.means3D, p.cam_pos, p.shs, p.clamped, p.dL_dcolor, p.dL_dsh);
         gmean.x += g.x; gmean.y += g.y; gmean.z += g.z;
@@ -619,43 +640,42 @@ __global__ void __launch_bounds__(256) geometry_backward_kernel(const GeomBackwa
     // ---- cov3D -> scale / rotation (backward.cu:278-341) ---------------------------------------
     if (p.scales != nullptr) {
         const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
-        const float r = q.x, x = q.y, y = q.z, z = q.w;
-        M3 R(1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-             2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-             2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
-        const float s[3] = {p.scale_modifier * p.scales[3 * idx], p.scale_modifier * p.scales[3 * idx + 1],
-                            p.scale_modifier * p.scales[3 * idx + 2]};
-        M3 Mm;   // M = S * R  ->  M[c][r] = s_r * R[c][r]
+        const real r = q.x, x = q.y, y = q.z, z = q.w;
+        // R[c][r_]: GLM storage of the reference's column-constructed matrix
+        const real R[3][3] = {{1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y)},
+                              {2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x)},
+                              {2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)}};
+        const real s[3] = {real(p.scale_modifier) * real(p.scales[3 * idx]), real(p.scale_modifier) * real(p.scales[3 * idx + 1]),
+                           real(p.scale_modifier) * real(p.scales[3 * idx + 2])};
+        real Mm[3][3];   // M = S * R  ->  M[c][r] = s_r * R[c][r]
 #pragma unroll
         for (int cc = 0; cc < 3; ++cc)
 #pragma unroll
-            for (int rr = 0; rr < 3; ++rr) Mm.c[cc][rr] = s[rr] * R.c[cc][rr];
-        M3 gS(gcov[0], 0.5f * gcov[1], 0.5f * gcov[2],
-              0.5f * gcov[1], gcov[3], 0.5f * gcov[4],
-              0.5f * gcov[2], 0.5f * gcov[4], gcov[5]);
-        M3 gM = m3_mul(Mm, gS);
+            for (int rr = 0; rr < 3; ++rr) Mm[cc][rr] = s[rr] * R[cc][rr];
+        const real gS[3][3] = {{gcov[0], real(0.5) * gcov[1], real(0.5) * gcov[2]},
+                               {real(0.5) * gcov[1], gcov[3], real(0.5) * gcov[4]},
+                               {real(0.5) * gcov[2], real(0.5) * gcov[4], gcov[5]}};
+        real gM[3][3];   // 2 * M * dL_dSigma with glm's operator*: (A*B)[c][r] = sum_k A[k][r] B[c][k]
 #pragma unroll
         for (int cc = 0; cc < 3; ++cc)
 #pragma unroll
-            for (int rr = 0; rr < 3; ++rr) gM.c[cc][rr] *= 2.0f;
+            for (int rr = 0; rr < 3; ++rr)
+                gM[cc][rr] = 2 * (Mm[0][rr] * gS[cc][0] + Mm[1][rr] * gS[cc][1] + Mm[2][rr] * gS[cc][2]);
         // gMt[i][j] = gM[j][i];  dL_dscale_i = sum_j R[j][i] * gM[j][i]
-        float gs[3];
 #pragma unroll
-        for (int i = 0; i < 3; ++i) gs[i] = R.c[0][i] * gM.c[0][i] + R.c[1][i] * gM.c[1][i] + R.c[2][i] * gM.c[2][i];
-        p.dL_dscale[3 * (size_t)idx + 0] = gs[0];
-        p.dL_dscale[3 * (size_t)idx + 1] = gs[1];
-        p.dL_dscale[3 * (size_t)idx + 2] = gs[2];
+        for (int i = 0; i < 3; ++i)
+            p.dL_dscale[3 * (size_t)idx + i] = (float)(R[0][i] * gM[0][i] + R[1][i] * gM[1][i] + R[2][i] * gM[2][i]);
         // A[i][j] = dL_dMt[i][j] * s_i   with dL_dMt[i][j] = gM[j][i]
-        float A[3][3];
+        real A[3][3];
 #pragma unroll
         for (int i = 0; i < 3; ++i)
 #pragma unroll
-            for (int j = 0; j < 3; ++j) A[i][j] = gM.c[j][i] * s[i];
+            for (int j = 0; j < 3; ++j) A[i][j] = gM[j][i] * s[i];
         float4 gq;
-        gq.x = 2 * z * (A[0][1] - A[1][0]) + 2 * y * (A[2][0] - A[0][2]) + 2 * x * (A[1][2] - A[2][1]);
-        gq.y = 2 * y * (A[1][0] + A[0][1]) + 2 * z * (A[2][0] + A[0][2]) + 2 * r * (A[1][2] - A[2][1]) - 4 * x * (A[2][2] + A[1][1]);
-        gq.z = 2 * x * (A[1][0] + A[0][1]) + 2 * r * (A[2][0] - A[0][2]) + 2 * z * (A[1][2] + A[2][1]) - 4 * y * (A[2][2] + A[0][0]);
-        gq.w = 2 * r * (A[0][1] - A[1][0]) + 2 * x * (A[2][0] + A[0][2]) + 2 * y * (A[1][2] + A[2][1]) - 4 * z * (A[1][1] + A[0][0]);
+        gq.x = (float)(2 * z * (A[0][1] - A[1][0]) + 2 * y * (A[2][0] - A[0][2]) + 2 * x * (A[1][2] - A[2][1]));
+        gq.y = (float)(2 * y * (A[1][0] + A[0][1]) + 2 * z * (A[2][0] + A[0][2]) + 2 * r * (A[1][2] - A[2][1]) - 4 * x * (A[2][2] + A[1][1]));
+        gq.z = (float)(2 * x * (A[1][0] + A[0][1]) + 2 * r * (A[2][0] - A[0][2]) + 2 * z * (A[1][2] + A[2][1]) - 4 * y * (A[2][2] + A[0][0]));
+        gq.w = (float)(2 * r * (A[0][1] - A[1][0]) + 2 * x * (A[2][0] + A[0][2]) + 2 * y * (A[1][2] + A[2][1]) - 4 * z * (A[1][1] + A[0][0]));
         reinterpret_cast<float4*>(p.dL_drot)[idx] = gq;
     }
 }

@@ -110,8 +110,11 @@ def test_stock_render_runs_unchanged_on_the_dropins(native_lib):
     for k in a:
         assert a[k].shape == b[k].shape and a[k].dtype == b[k].dtype, k
     assert torch.equal(a["radii"], b["radii"]) and torch.equal(a["visibility_filter"], b["visibility_filter"])
-    for k in ("depth", "normal", "alpha", "normal_ref"):      # pure rasterizer outputs of identical inputs
+    for k in ("depth", "normal", "alpha"):                    # pure rasterizer outputs of identical inputs
         _close_img(a[k], b[k], k, 2e-5 * max(1.0, a[k].abs().max().item()))
+    # normal_ref = normalised cross product of DIFFERENCES of neighbouring back-projected depths (both arms run the
+    # reference's own depth_to_normal here): a 1e-6 relative depth difference is amplified ~100x
+    _close_img(a["normal_ref"], b["normal_ref"], "normal_ref", 5e-4)
     for k in ("render", "diffuse_color", "specular_color"):   # + fused shading vs the torch graph (1e-5 relative colours)
         _close_img(a[k], b[k], k, 3e-5)
     names = ["xyz", "scaling", "rotation", "opacity", "albedo", "roughness", "metalness", "sky_angles", "env_sh",
