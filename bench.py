@@ -48,6 +48,7 @@ def parse_args():
                     help="BASELINE.json config C: V views per step in TOTAL, sharded over the ranks (rank r renders views "
                          "r, r+N, ...; gradients accumulate, ONE all-reduce, densification statistics all-reduced): strong "
                          "scaling.  0 (default): one view per rank per step, weak scaling")
+    ap.add_argument("--quick", action="store_true", help="timed step + e2e only (no U1 / U3 / fused / stock / profile extras)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
     return ap.parse_args()
@@ -757,6 +758,15 @@ def main():
             line["config"]["caller"] = ("oracle/_ref/py absent: the repo's render() mirror + oracle/ restatements of the "
                                         "reference torch graphs around the reference extension")
 
+    if args.quick:
+        if rank == 0:
+            line["step_ms"] = [round(x, 2) for x in LAST_STEP_MS]
+            print(json.dumps(line))
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
     # ---- extras: fwd-only frames/s (U3), single raster call fwd / fwd+bwd (U1) ---------------------------
     def frame(new_view=True):
         if new_view and args.impl == "native":
@@ -809,6 +819,15 @@ def main():
             line["stock_render_on_dropins"] = {"value": 1e3 / ms_s, "unit": UNIT, "ms_per_step": ms_s, "n_gpus": 1,
                                                "api": "reference gaussian_renderer.render() + GaussianModel getters, "
                                                       "drop-in rasterizer / EnvironmentLight / loss functions"}
+            # attribution only: the same with render()'s torch.cuda.empty_cache() (gaussian_renderer/__init__.py:237)
+            # patched out - every step otherwise hands all cached blocks back to the driver and re-cudaMallocs them
+            real_empty = torch.cuda.empty_cache
+            try:
+                torch.cuda.empty_cache = lambda: None
+                ms_n = timed_steps(torch, lambda: st_s.step(gt), nfz, 4, flush, None) / nfz
+            finally:
+                torch.cuda.empty_cache = real_empty
+            line["stock_render_on_dropins"]["ms_per_step_without_empty_cache"] = ms_n
             del st_s
         except (SystemExit, Exception) as e:   # noqa: BLE001
             line["stock_render_on_dropins"] = {"unavailable": str(e)[:200]}

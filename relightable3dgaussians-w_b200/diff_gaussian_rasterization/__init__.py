@@ -80,22 +80,44 @@ def _stream():
     return _nat.raw_stream()
 
 
+# Largest request seen per (role, device).  The binning buffer's size follows R, which differs from view to view:
+# asking torch's caching allocator for a slightly different multi-hundred-MB block every frame makes it split and
+# re-grow its large blocks until the device is full and it has to release everything (seen as 30-80 ms single-step
+# stalls with 8 views per step).  Requests are therefore rounded up to the high-water mark (+ 6 % headroom when it
+# grows): after one pass over the views every frame asks for the same size and gets the same block back.
+_size_hwm = {}
+
+
 class _Holder:
     """Allocation-callback target: the library asks for bytes, torch owns them."""
 
-    def __init__(self, device):
+    def __init__(self, device, role=None):
         self.device = device
         self.t = None
 
+        _nbytes_exact = [0]
+
         def _cb(_ctx, nbytes):
+            nbytes = int(nbytes)
+            _nbytes_exact[0] = nbytes
+            if role is not None and nbytes > (1 << 20):
+                key = (role, self.device)
+                hwm = _size_hwm.get(key, 0)
+                if nbytes > hwm:
+                    hwm = (nbytes + nbytes // 16 + (1 << 21) - 1) >> 21 << 21
+                    _size_hwm[key] = hwm
+                nbytes = hwm
             for attempt in (0, 1):
                 try:
-                    self.t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
+                    self.t = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=self.device)
                     return self.t.data_ptr()
                 except torch.OutOfMemoryError:
                     if attempt == 0:        # multi-GB state buffers: give cached-but-fragmented blocks back and retry once
                         clear_geometry_cache()
                         torch.cuda.empty_cache()
+                        if role is not None:
+                            _size_hwm.pop((role, self.device), None)
+                            nbytes = int(_nbytes_exact[0])
                 except Exception:   # noqa: BLE001 - surfaces as R3DGW_ERR_ALLOC
                     break
             return 0
@@ -200,7 +222,7 @@ def _run_geometry(means3D, opacities, scales, rotations, cov3D_precomp, sh, sett
     cam, keep = _make_camera(settings, device)
     st.cam, st.keep = cam, keep
     st.radii = torch.zeros(st.P, dtype=torch.int32, device=device)
-    gh, bh = _Holder(device), _Holder(device)
+    gh, bh = _Holder(device, "geometry"), _Holder(device, "binning")
     R = ctypes.c_int(0)
     with _nat.on_device(device):
         rc = L.r3dgw_geometry_forward(gh.cb, None, bh.cb, None, st.P, int(settings.sh_degree), M,

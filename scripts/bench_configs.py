@@ -199,12 +199,15 @@ def config_E():
             if bwd:
                 img.backward(dL)
             return radii
-        radii = call(False)
-        fwd, _ = timed(lambda: call(False), 5, 2)
-        fb, _ = timed(lambda: call(True), 5, 2)
-        out[tag] = {"fwd_ms": fwd, "fwd_bwd_ms": fb, "P_visible": int((radii > 0).sum())}
-        if mod is dgr:
-            out[tag]["R"] = int(dgr.last_geometry_state().R)
+        try:
+            radii = call(False)
+            fwd, _ = timed(lambda: call(False), 5, 2)
+            fb, _ = timed(lambda: call(True), 5, 2)
+            out[tag] = {"fwd_ms": fwd, "fwd_bwd_ms": fb, "P_visible": int((radii > 0).sum())}
+            if mod is dgr:
+                out[tag]["R"] = int(dgr.last_geometry_state().R)
+        except Exception as e:   # noqa: BLE001 - the reference's own limits are part of the record
+            out[tag] = {"failed": f"{type(e).__name__}: {str(e)[:200]}"}
         torch.cuda.empty_cache()
     print(json.dumps(out))
 

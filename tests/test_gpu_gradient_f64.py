@@ -6,9 +6,13 @@ backward.cu:144-557 with every decision taken in float exactly as the reference 
 double, evaluated over the reference's OWN forward buffers.  Enforced per gradient tensor, at configs small, A and
 B (the config every bench number is quoted on), for the single U1 call and for render()'s six-call pattern:
 
-    ||new - f64||_2 <= 1e-3 ||f64||_2                  (north_star: gradients <= 1e-3 relative)
+    ||new - f64||_2 <= 1e-4 ||f64||_2                  (north_star asks <= 1e-3 relative; measured: <= 2.2e-5)
     ||new - f64||_2 <= 1.5 ||ref - f64||_2 + 1e-6 ||f64||_2   (never less accurate than the reference's own kernels)
-    99.9 % of entries: |new - f64| <= 1e-3 |f64| + 1e-5 max|f64|
+    99.99 % of entries: |new - f64| <= 1e-3 |f64| + 1e-5 max|f64|
+(The reference itself sits at 6e-4 .. 1e-3 on rotations and 1e-4 .. 2e-4 on scales at A / B: its float evaluation of
+the cov2D -> cov3D -> quaternion chain cancels heavily.  The new fused geometry backward evaluates that chain in FP64
+- the kernel is HBM-bound - and lands 40-60x closer to the FP64 truth; screen-space gradients, whose error is the
+float accumulation order, are level with the reference.)
 
 The measured errors of both implementations are printed (pytest -s) and kept in profiles/r02_grad_f64.txt.
 """
@@ -61,11 +65,11 @@ def _check(name, new, ref, f64, report):
     report.append(f"{name:<12} ||f64|| {nf:.4e}  new-f64 {e_new / nf:.3e}  ref-f64 {e_ref / nf:.3e}  "
                   f"new/ref {e_new / max(e_ref, 1e-300):.2f}  entries within strict bar {strict:.6f}")
     bad = []
-    if not e_new <= 1e-3 * nf:
-        bad.append(f"{name}: relative L2 error vs FP64 {e_new / nf:.3e} > 1e-3")
+    if not e_new <= 1e-4 * nf:
+        bad.append(f"{name}: relative L2 error vs FP64 {e_new / nf:.3e} > 1e-4")
     if not e_new <= 1.5 * e_ref + 1e-6 * nf:
         bad.append(f"{name}: new {e_new / nf:.3e} vs reference {e_ref / nf:.3e} (FP64 oracle)")
-    if not strict >= 0.999:
+    if not strict >= 0.9999:
         bad.append(f"{name}: only {strict:.5f} of entries within 1e-3 relative + 1e-5 of scale")
     return bad
 

@@ -587,3 +587,65 @@ def test_alpha_cache_replay_is_bit_exact(native_lib, name, kw):
         assert torch.equal(a, b), f"blend #{k + 1}"
     for k, (a, b) in enumerate(zip(on_grads, off_grads)):   # same kernels, same inputs: only atomic order differs
         _grad_close(a, b, f"grad[{k}]")
+
+
+@pytest.mark.parametrize("name", ["small", "A", "B"])
+def test_alpha_cache_stays_inside_its_buffer(native_lib, name):
+    """compute-sanitizer is not available on the GPU pool, so the alpha cache's bounds are checked with canaries:
+    the record / replay / colour-only-backward kernels get a cache pointer INSIDE a larger buffer whose guard zones
+    (64 MiB either side) are filled with NaN.  After record + replay + backward the guards must be bit-identical
+    (nothing written outside [0, r3dgw_alpha_cache_bytes(R))) and every output must equal, bit for bit, the run on a
+    zero-padded buffer (no guard value was ever read and used)."""
+    import ctypes
+    import diff_gaussian_rasterization as dgr
+    from r3dgw_b200 import native
+    from r3dgw_b200.synthetic import make_scene
+    sc = make_scene(name).to("cuda")
+    s = _settings(dgr, sc)
+    H, W, P = s.image_height, s.image_width, sc.P
+    dgr.clear_geometry_cache()
+    with torch.no_grad():
+        dgr.GaussianRasterizer(s)(means3D=sc.means3D, means2D=torch.zeros_like(sc.means3D), opacities=sc.opacities,
+                                  colors_precomp=sc.colors, scales=sc.scales, rotations=sc.rotations)
+    st = dgr.last_geometry_state()
+    L = native.lib()
+    nbytes = int(L.r3dgw_alpha_cache_bytes(st.R))
+    assert nbytes == st.R * 1024
+    guard = 64 << 20
+    IL = native.ImageLayout()
+    L.r3dgw_get_image_layout(W, H, ctypes.byref(IL))
+    gen = torch.Generator().manual_seed(5)
+    dL = (torch.randn(3, H, W, generator=gen) * 1e-3).cuda()
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def run(poison):
+        buf = torch.zeros(guard + nbytes + guard, dtype=torch.uint8, device="cuda")
+        if poison:
+            buf.view(torch.int32)[: guard // 4] = 0x7FC00000
+            buf.view(torch.int32)[(guard + nbytes) // 4:] = 0x7FC00000
+        cache = buf.data_ptr() + guard
+        img = torch.zeros(IL.total, dtype=torch.uint8, device="cuda")
+        outs = []
+        for mode in (1, 2):
+            out = torch.zeros(3, H, W, device="cuda")
+            rc = L.r3dgw_blend_forward_cached(P, st.R, 3, ctypes.byref(st.cam), st.geom.data_ptr(), st.binning.data_ptr(),
+                                              img.data_ptr(), sc.colors.data_ptr(), sc.bg.data_ptr(), out.data_ptr(), cache,
+                                              mode, stream)
+            assert rc == 0
+            outs.append(out)
+        dfeat = torch.zeros(P, 4, device="cuda")
+        rc = L.r3dgw_blend_backward_color_cached(P, st.R, 3, ctypes.byref(st.cam), st.binning.data_ptr(), img.data_ptr(),
+                                                 cache, dL.data_ptr(), dfeat.data_ptr(), 4, stream)
+        assert rc == 0
+        torch.cuda.synchronize()
+        lo = buf.view(torch.int32)[: guard // 4]
+        hi = buf.view(torch.int32)[(guard + nbytes) // 4:]
+        return outs, dfeat, lo, hi
+
+    (rec_p, rep_p), df_p, lo, hi = run(True)
+    assert bool((lo == 0x7FC00000).all()) and bool((hi == 0x7FC00000).all()), "alpha cache written outside its bytes"
+    (rec_z, rep_z), df_z, _, _ = run(False)
+    assert torch.equal(rec_p, rec_z) and torch.equal(rep_p, rep_z) and torch.equal(rec_p, rep_p)
+    assert not bool(torch.isnan(df_p).any())
+    # atomics reorder the float sums of the gradient: NaN-free and equal up to that
+    _grad_close(df_p[:, :3], df_z[:, :3], "colour gradient with poisoned guards")
