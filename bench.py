@@ -234,9 +234,12 @@ class Stepper:
             loss_sky = ops.l1_loss(out["diffuse_color"], torch.zeros_like(out["diffuse_color"]), mask=1 - sky3) + \
                 ops.l1_loss(out["specular_color"], torch.zeros_like(out["specular_color"]), mask=1 - sky3)
         loss = loss + LAMBDA["sky_brdf"] * loss_sky
-        rn = out["normal"] * occl3 * sky3
-        rs = out["normal_ref"] * occl3 * sky3
-        loss = loss + LAMBDA["normal"] * (1 - (rn * rs).sum(dim=0))[None].mean()
+        if self.impl == "native":
+            loss = loss + LAMBDA["normal"] * ops.normal_consistency_loss(out["normal"], out["normal_ref"], occl1, sky2)
+        else:
+            rn = out["normal"] * occl3 * sky3
+            rs = out["normal_ref"] * occl3 * sky3
+            loss = loss + LAMBDA["normal"] * (1 - (rn * rs).sum(dim=0))[None].mean()
         # min_scale_loss (utils/loss_utils.py:210-220) and depth_loss_gaussians (:140-148)
         if self.impl == "native":
             # one masked fixed-order reduction each way, no boolean-mask gathers / sort / host syncs
@@ -378,6 +381,7 @@ def l2_flush(torch, buf):
 
 RANK0_SAMPLES = int(os.environ.get("RANK", "0")) == 0     # clocks are sampled by rank 0 only: 8 processes querying
 # NVML in the same step serialise in the driver (r01: 85-100 ms single-step stalls at N = 8)
+SAMPLE_EVERY_STEP = os.environ.get("R3DGW_BENCH_SAMPLE_EVERY", "0") == "1"      # diagnostics: clocks / reasons per step
 LAST_STEP_MS = []      # per-step device times of the most recent timed_steps() call (diagnostics on stderr)
 
 
@@ -401,7 +405,7 @@ def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None, sampler=None):
         a.record()
         fn()
         b.record()
-        if sampler is not None and len(sampler.samples) < 6 and k % 4 == 1 and RANK0_SAMPLES:
+        if sampler is not None and RANK0_SAMPLES and (SAMPLE_EVERY_STEP or (len(sampler.samples) < 6 and k % 4 == 1)):
             sampler.sample()      # GPU still busy with the step just enqueued; outside every event pair
     torch.cuda.synchronize()
     if dist is not None:
@@ -544,6 +548,8 @@ def main():
     dist = None
     if world > 1 and args.impl == "native":
         import torch.distributed as dist_mod
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"       # NCCL prints its version banner on stdout: keep stdout to the one JSON line
         dist_mod.init_process_group("nccl", device_id=device)
         dist = dist_mod
 
@@ -608,7 +614,7 @@ def main():
             bucket.all_reduce(average_over=V)
             sync_densification_stats(dens["accum"], dens["denom"], dens["max_radii"])
 
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank) if os.environ.get("R3DGW_BENCH_NO_SAMPLER", "0") != "1" else None
     # setup (not part of W): iterations so that torch's caching allocator has grown its pools (the first ones
     # otherwise pay cudaMalloc, a device-wide sync each, inside the step) and so that the timed region starts in
     # the sustained regime: on this pool the first ~100 ms of back-to-back steps run ~7 % faster than steady state
@@ -619,10 +625,19 @@ def main():
         step_resident()
     torch.cuda.synchronize()
     launches0 = L.r3dgw_launch_count() if L else 0
+    ms0 = torch.cuda.memory_stats(device)
     total_ms = timed_steps(torch, step_resident, args.steps, 0, flush, dist, sampler)
+    ms1 = torch.cuda.memory_stats(device)
+    allocator = {"cudaMalloc_calls_in_timed_region": int(ms1.get("num_device_alloc", 0) - ms0.get("num_device_alloc", 0)),
+                 "cudaFree_calls_in_timed_region": int(ms1.get("num_device_free", 0) - ms0.get("num_device_free", 0)),
+                 "alloc_retries": int(ms1.get("num_alloc_retries", 0)),
+                 "reserved_gb": round(ms1.get("reserved_bytes.all.current", 0) / 2**30, 2),
+                 "peak_allocated_gb": round(ms1.get("allocated_bytes.all.peak", 0) / 2**30, 2)}
     if rank == 0:
         print("step ms (resident):", [round(x, 2) for x in LAST_STEP_MS], file=sys.stderr)
-    clocks = sampler.summary()
+        if SAMPLE_EVERY_STEP and sampler is not None:
+            print("per-step (sm_mhz, power_w, reasons):", [(int(a), int(b), hex(c)) for a, b, c in sampler.samples], file=sys.stderr)
+    clocks = sampler.summary() if sampler is not None else {"sm_mhz": None, "reasons": ["sampler disabled (R3DGW_BENCH_NO_SAMPLER=1)"]}
     gpu_launches = (L.r3dgw_launch_count() - launches0) if L else 0
     ms_per_step = total_ms / args.steps
     value = world * 1e3 / ms_per_step if args.impl == "native" else 1e3 / ms_per_step
@@ -638,7 +653,7 @@ def main():
                                        f"(rank r renders views r, r+N, ...), gradient accumulation, one all-reduce of the "
                                        f"parameter gradients (ReduceOp.SUM + 1/V) and of the densification statistics per step",
                            "mode": args.mode, "l2": "512 MiB flush between timed steps"},
-                "clocks": clocks, "gpu_launches": int(gpu_launches), "impl": args.impl,
+                "clocks": clocks, "gpu_launches": int(gpu_launches), "impl": args.impl, "allocator": allocator,
                 "step_ms": [round(x, 2) for x in LAST_STEP_MS]}))
         if dist is not None:
             dist.barrier()
@@ -739,7 +754,7 @@ def main():
                        "mode": args.mode, "views_per_step": world,
                        "caller": ("reference render() + train.py loss, unmodified (oracle/_ref/py)" if isinstance(st, StockStepper)
                                   else "r3dgw_b200.render (the repo's render() / render_fused(), reference call pattern)")},
-            "clocks": clocks, "gpu_launches": int(gpu_launches),
+            "clocks": clocks, "gpu_launches": int(gpu_launches), "allocator": allocator,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": 4, "h2d_gbps_measured": round(h2d_gbps, 2),
                     "loss_read": "this step's loss is copied D2H right after its forward pass and read on the host "
@@ -882,8 +897,19 @@ def main():
                 traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))[top]["dram_traffic_bytes_per_launch"]
         except Exception:   # noqa: BLE001
             pass
+        # SURVEY 8(d)'s closed forms for the REFERENCE algorithm's compulsory bytes of the same stage: a replay kernel reads
+        # its alphas from HBM instead of recomputing them, so the bytes it must move (above) exceed these
+        survey = {"blend_forward_cached": (28 + 4 * 3) * Rn + (4 * 3 + 8) * N,
+                  "blend_backward_color_cached": (28 + 4 * 3) * Rn + (4 * 3 + 8) * N + (4 * 3 + 24) * Pv}
+        ab_survey = survey.get(top, _ab(top, P, Pv, Rn, N, tiles, C, n_pass))
         line["roofline"] = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s",
                             "frac": ach / peak, "traffic": traffic,
+                            "frac_algorithmic": ab_survey / (kern[top]["avg_launch_ms"] * 1e-3) / 1e9 / peak,
+                            "survey_8d_bytes_per_launch": ab_survey,
+                            "traffic_over_algorithmic": (traffic / ab_survey) if traffic else ab / ab_survey,
+                            "frac_definition": "frac: bytes this kernel must move (alpha-cache rows it replays + streams) / "
+                                               "time / peak; frac_algorithmic: SURVEY 8(d) compulsory bytes of the "
+                                               "reference stage it replaces / time / peak",
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650",
                             "algorithmic_bytes_per_launch": ab, "avg_launch_ms": kern[top]["avg_launch_ms"],
                             "share_of_step_kernel_time": kern[top]["ms_per_step"] / step_kernel_ms}

@@ -353,6 +353,25 @@ int r3dgw_depth_to_normal_forward(int H, int W, const float* depth, const float*
 int r3dgw_depth_to_normal_backward(int H, int W, const float* depth, const float* rays, const float* dL_dnormal,
                                    float* dL_ddepth, void* stream);
 
+/* image-space tail of render() (gaussian_renderer/__init__.py:231-237, 266-271), one kernel each way:
+ *   normal     = ((n01 - 0.5) * 2) * sky + (1 - sky)            n01: rasterized 0.5 n + 0.5 image, f32[3,H,W]
+ *   normal_ref = depth_to_normal(depth * sky) * alpha + (1 - sky)  depth / alpha: f32[H,W] (channel 0 of the images)
+ * rays: the 21 floats of r3dgw_depth_to_normal_*.  alpha is treated as a constant (the reference detaches it).
+ * backward: any of dL_dnormal / dL_dnormal_ref may be NULL (zero); outputs dL_dn01 f32[3,H,W], dL_ddepth f32[H,W]. */
+int r3dgw_normal_tail_forward(int H, int W, const float* n01, const float* depth, const float* alpha, const float* sky,
+                              const float* rays, float* normal, float* normal_ref, void* stream);
+int r3dgw_normal_tail_backward(int H, int W, const float* depth, const float* alpha, const float* sky, const float* rays,
+                               const float* dL_dnormal, const float* dL_dnormal_ref, float* dL_dn01, float* dL_ddepth,
+                               void* stream);
+/* normal-consistency term (train.py:92-96): out[0] = mean over the H*W pixels of
+ * 1 - sum_c (normal_c occl sky)(normal_ref_c occl sky); occl / sky f32[H,W] or NULL (ones); fixed-order reduction.
+ * workspace: r3dgw_image_loss_workspace_bytes(1,H,W).  backward: coef = device f32[1] upstream gradient. */
+int r3dgw_normal_loss_forward(int H, int W, const float* normal, const float* normal_ref, const float* occl,
+                              const float* sky, char* workspace, float* out, void* stream);
+int r3dgw_normal_loss_backward(int H, int W, const float* normal, const float* normal_ref, const float* occl,
+                               const float* sky, const float* coef, float* dL_dnormal, float* dL_dnormal_ref,
+                               void* stream);
+
 /* ---- host side of the eval grid on the device -----------------------------------
  * Replace numpy / cv2 / spaudiopy host code in the reference (paths relative to /root/reference):
  *   r3dgw_envmap_resize_cubic <- utils/sh_additional_utils.py:48-70 (resize_image -> cv2.resize INTER_CUBIC, the

@@ -391,6 +391,149 @@ __global__ void __launch_bounds__(256) depth_to_normal_backward_kernel(int H, in
     dL_ddepth[(size_t)y * W + x] = acc;
 }
 
+// ---- image-space tail of render() + the normal-consistency term, fused ----------------------------------
+// gaussian_renderer/__init__.py:231-237, 266-271 on the rasterized normal / depth / alpha images:
+//     normal     = ((n01 - 0.5) * 2) * sky + 1 * (1 - sky)
+//     normal_ref = depth_to_normal(view, depth[0] * sky).permute(2,0,1) * alpha.detach() + 1 * (1 - sky)
+// one thread per pixel, same expression order as the torch ops (the depth fed to depth_to_normal is the MASKED depth of
+// every neighbour); a dozen elementwise launches + the permute each way become one kernel each way.
+__device__ __forceinline__ float3 world_point_m(const float* __restrict__ depth, const float* __restrict__ sky, const float* M,
+                                                int W, int x, int y) {
+    const size_t i = (size_t)y * W + x;
+    const float d = __fmul_rn(depth[i], sky[i]);
+    const float3 r = ray_dir(M, x, y);
+    const float* o = M + 18;
+    return make_float3(__fadd_rn(__fmul_rn(d, r.x), o[0]), __fadd_rn(__fmul_rn(d, r.y), o[1]),
+                       __fadd_rn(__fmul_rn(d, r.z), o[2]));
+}
+__device__ __forceinline__ void normal_diffs_m(const float* __restrict__ depth, const float* __restrict__ sky, const float* M,
+                                               int W, int x, int y, float3& dx, float3& dy) {
+    const float3 pu = world_point_m(depth, sky, M, W, x, y + 1), pd = world_point_m(depth, sky, M, W, x, y - 1);
+    const float3 pr = world_point_m(depth, sky, M, W, x + 1, y), pl = world_point_m(depth, sky, M, W, x - 1, y);
+    dx = make_float3(pu.x - pd.x, pu.y - pd.y, pu.z - pd.z);
+    dy = make_float3(pr.x - pl.x, pr.y - pl.y, pr.z - pl.z);
+}
+
+__global__ void __launch_bounds__(256) normal_tail_forward_kernel(
+    int H, int W, const float* __restrict__ n01, const float* __restrict__ depth, const float* __restrict__ alpha,
+    const float* __restrict__ sky, const float* __restrict__ rays, float* __restrict__ normal, float* __restrict__ normal_ref) {
+    __shared__ float M[RAYS_N];
+    if (threadIdx.x < RAYS_N) M[threadIdx.x] = rays[threadIdx.x];
+    __syncthreads();
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= W || y >= H) return;
+    const size_t plane = (size_t)H * W, i = (size_t)y * W + x;
+    const float m = sky[i], one_m = __fsub_rn(1.f, m);
+    float3 n = make_float3(0.f, 0.f, 0.f);
+    if (x >= 1 && x < W - 1 && y >= 1 && y < H - 1) {
+        float3 dx, dy;
+        normal_diffs_m(depth, sky, M, W, x, y, dx, dy);
+        const float3 v = cross3(dx, dy);
+        const float len = fmaxf(sqrtf(dot3(v, v)), 1e-12f);
+        n = make_float3(v.x / len, v.y / len, v.z / len);
+    }
+    const float a = alpha[i];
+    const float nr[3] = {n.x, n.y, n.z};
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float v = __fmul_rn(__fsub_rn(n01[c * plane + i], 0.5f), 2.0f);
+        normal[c * plane + i] = __fadd_rn(__fmul_rn(v, m), one_m);
+        normal_ref[c * plane + i] = __fadd_rn(__fmul_rn(nr[c], a), one_m);
+    }
+}
+
+// gradient of the (alpha-weighted) normal at interior pixel (cx, cy) w.r.t. its dx / dy vectors; g planar [3,H,W]
+__device__ __forceinline__ void normal_backprop_m(const float* __restrict__ depth, const float* __restrict__ sky,
+                                                  const float* M, const float* __restrict__ g_ref,
+                                                  const float* __restrict__ alpha, int W, size_t plane, int cx, int cy,
+                                                  float3& g_dx, float3& g_dy) {
+    float3 dx, dy;
+    normal_diffs_m(depth, sky, M, W, cx, cy, dx, dy);
+    const float3 v = cross3(dx, dy);
+    const float len = sqrtf(dot3(v, v));
+    const size_t j = (size_t)cy * W + cx;
+    const float a = alpha[j];
+    const float3 g = make_float3(g_ref[j] * a, g_ref[plane + j] * a, g_ref[2 * plane + j] * a);
+    float3 u;
+    if (len > 1e-12f) {
+        const float inv = 1.f / len;
+        const float3 n = make_float3(v.x * inv, v.y * inv, v.z * inv);
+        const float ng = dot3(n, g);
+        u = make_float3((g.x - n.x * ng) * inv, (g.y - n.y * ng) * inv, (g.z - n.z * ng) * inv);
+    } else {
+        u = make_float3(g.x * 1e12f, g.y * 1e12f, g.z * 1e12f);
+    }
+    g_dx = cross3(dy, u);
+    g_dy = cross3(u, dx);
+}
+
+__global__ void __launch_bounds__(256) normal_tail_backward_kernel(
+    int H, int W, const float* __restrict__ depth, const float* __restrict__ alpha, const float* __restrict__ sky,
+    const float* __restrict__ rays, const float* __restrict__ g_normal, const float* __restrict__ g_ref,
+    float* __restrict__ g_n01, float* __restrict__ g_depth) {
+    __shared__ float M[RAYS_N];
+    if (threadIdx.x < RAYS_N) M[threadIdx.x] = rays[threadIdx.x];
+    __syncthreads();
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= W || y >= H) return;
+    const size_t plane = (size_t)H * W, i = (size_t)y * W + x;
+    const float m = sky[i];
+    if (g_n01) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) g_n01[c * plane + i] = g_normal ? (g_normal[c * plane + i] * m) * 2.0f : 0.f;
+    }
+    if (g_depth) {
+        float acc = 0.f;
+        if (g_ref) {
+            const float3 r = ray_dir(M, x, y);
+            float3 gdx, gdy;
+            auto interior = [&](int cx, int cy) { return cx >= 1 && cx < W - 1 && cy >= 1 && cy < H - 1; };
+            if (interior(x, y - 1)) { normal_backprop_m(depth, sky, M, g_ref, alpha, W, plane, x, y - 1, gdx, gdy); acc += dot3(r, gdx); }
+            if (interior(x, y + 1)) { normal_backprop_m(depth, sky, M, g_ref, alpha, W, plane, x, y + 1, gdx, gdy); acc -= dot3(r, gdx); }
+            if (interior(x - 1, y)) { normal_backprop_m(depth, sky, M, g_ref, alpha, W, plane, x - 1, y, gdx, gdy); acc += dot3(r, gdy); }
+            if (interior(x + 1, y)) { normal_backprop_m(depth, sky, M, g_ref, alpha, W, plane, x + 1, y, gdx, gdy); acc -= dot3(r, gdy); }
+        }
+        g_depth[i] = acc * m;          // depth enters as depth * sky
+    }
+}
+
+// normal-consistency term of train.py:92-96: mean over pixels of 1 - sum_c (normal_c w)(normal_ref_c w), w = occl * sky
+__global__ void __launch_bounds__(IMG_THREADS) normal_loss_forward_kernel(
+    size_t plane, const float* __restrict__ normal, const float* __restrict__ normal_ref,
+    const float* __restrict__ occl, const float* __restrict__ sky, float* __restrict__ partials) {
+    __shared__ float red[3][IMG_WARPS];
+    float acc = 0.f, cnt = 0.f;
+    for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < plane; i += (size_t)gridDim.x * IMG_THREADS) {
+        const float o = occl ? occl[i] : 1.f, m = sky ? sky[i] : 1.f;
+        float d = 0.f;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float rn = (normal[c * plane + i] * o) * m, rs = (normal_ref[c * plane + i] * o) * m;
+            d += rn * rs;
+        }
+        acc += 1.f - d;
+        cnt += 1.f;
+    }
+    block_partials3(acc, 0.f, cnt, red, partials + (size_t)blockIdx.x * 3);
+}
+
+__global__ void __launch_bounds__(IMG_THREADS) normal_loss_backward_kernel(
+    size_t plane, const float* __restrict__ normal, const float* __restrict__ normal_ref,
+    const float* __restrict__ occl, const float* __restrict__ sky, const float* __restrict__ coef,
+    float* __restrict__ g_normal, float* __restrict__ g_ref) {
+    const float k = -coef[0] / (float)plane;
+    for (size_t i = (size_t)blockIdx.x * IMG_THREADS + threadIdx.x; i < plane; i += (size_t)gridDim.x * IMG_THREADS) {
+        const float o = occl ? occl[i] : 1.f, m = sky ? sky[i] : 1.f;
+        const float w2 = k * (o * m) * (o * m);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float a = normal[c * plane + i], b = normal_ref[c * plane + i];
+            if (g_normal) g_normal[c * plane + i] = w2 * b;
+            if (g_ref) g_ref[c * plane + i] = w2 * a;
+        }
+    }
+}
+
 // blocks per channel plane: 16 pixels per thread, at most NUM_SMS * 8 blocks over all channels (the workspace bound)
 static inline int l1_blocks(size_t plane, int C) {
     size_t b = (plane + IMG_THREADS * 16 - 1) / (IMG_THREADS * 16);
@@ -487,6 +630,66 @@ int r3dgw_masked_l1_backward(int C, int H, int W, const float* x, const float* t
         else
             masked_l1_backward_kernel<false><<<grid, IMG_THREADS, 0, stream>>>(plane, x, target, mask, mask_channel_stride,
                                                                                complement, sums, coef, dL_dx);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_normal_tail_forward(int H, int W, const float* n01, const float* depth, const float* alpha, const float* sky,
+                              const float* rays, float* normal, float* normal_ref, void* stream_) {
+    if (H <= 0 || W <= 0 || !n01 || !depth || !alpha || !sky || !rays || !normal || !normal_ref) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    dim3 grid((W + 31) / 32, (H + 7) / 8);
+    {
+        ProfScope ps(KID_DEPTH_NORMAL, stream);
+        normal_tail_forward_kernel<<<grid, 256, 0, stream>>>(H, W, n01, depth, alpha, sky, rays, normal, normal_ref);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_normal_tail_backward(int H, int W, const float* depth, const float* alpha, const float* sky, const float* rays,
+                               const float* dL_dnormal, const float* dL_dnormal_ref, float* dL_dn01, float* dL_ddepth,
+                               void* stream_) {
+    if (H <= 0 || W <= 0 || !depth || !alpha || !sky || !rays) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    dim3 grid((W + 31) / 32, (H + 7) / 8);
+    {
+        ProfScope ps(KID_DEPTH_NORMAL, stream);
+        normal_tail_backward_kernel<<<grid, 256, 0, stream>>>(H, W, depth, alpha, sky, rays, dL_dnormal, dL_dnormal_ref,
+                                                              dL_dn01, dL_ddepth);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_normal_loss_forward(int H, int W, const float* normal, const float* normal_ref, const float* occl,
+                              const float* sky, char* workspace, float* out, void* stream_) {
+    if (H <= 0 || W <= 0 || !normal || !normal_ref || !workspace || !out) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const size_t plane = (size_t)H * W;
+    const int blocks = l1_blocks(plane, 1);
+    float* partials = reinterpret_cast<float*>(workspace);
+    {
+        ProfScope ps(KID_MASKED_L1, stream);
+        normal_loss_forward_kernel<<<blocks, IMG_THREADS, 0, stream>>>(plane, normal, normal_ref, occl, sky, partials);
+    }
+    R3DGW_LAUNCH_CHECK();
+    loss_finalize_kernel<<<1, 256, 0, stream>>>(partials, blocks, out);       // out[0] = mean over the H*W pixels
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int r3dgw_normal_loss_backward(int H, int W, const float* normal, const float* normal_ref, const float* occl,
+                               const float* sky, const float* coef, float* dL_dnormal, float* dL_dnormal_ref,
+                               void* stream_) {
+    if (H <= 0 || W <= 0 || !normal || !normal_ref || !coef) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const size_t plane = (size_t)H * W;
+    {
+        ProfScope ps(KID_MASKED_L1, stream);
+        normal_loss_backward_kernel<<<l1_blocks(plane, 1), IMG_THREADS, 0, stream>>>(plane, normal, normal_ref, occl, sky,
+                                                                                      coef, dL_dnormal, dL_dnormal_ref);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;

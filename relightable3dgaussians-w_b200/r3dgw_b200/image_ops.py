@@ -211,3 +211,102 @@ def depth_to_normal(view, depth, rays=None):
     if rays is None:
         rays = ray_basis(view)
     return _DepthToNormalFn.apply(depth, rays.detach())
+
+
+# r3dgw_b200.render.render() / render_fused() given THIS depth_to_normal run the whole image-space tail as one fused
+# kernel (normal_tail below) instead of the reference's chain of elementwise ops around it
+depth_to_normal.fused_tail = True
+
+
+class _NormalTailFn(torch.autograd.Function):
+    """(n01 image, depth image, alpha image, sky mask) -> (normal, normal_ref): the image-space tail of render()
+    (gaussian_renderer/__init__.py:231-237, 266-271) in one kernel each way."""
+
+    @staticmethod
+    def forward(ctx, n01, depth_img, alpha_img, sky, rays):
+        _require_cuda(n01, "normal_tail")
+        n = _f32c(n01)
+        H, W = int(n.shape[-2]), int(n.shape[-1])
+        d = _f32c(depth_img.reshape(-1, H, W)[0])
+        a = _f32c(alpha_img.reshape(-1, H, W)[0])
+        m = _f32c(sky.reshape(H, W))
+        out = torch.empty(2, 3, H, W, dtype=torch.float32, device=n.device)
+        with _nat.on_device(n.device):
+            rc = _nat.lib().r3dgw_normal_tail_forward(H, W, n.data_ptr(), d.data_ptr(), a.data_ptr(), m.data_ptr(),
+                                                      rays.data_ptr(), out[0].data_ptr(), out[1].data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_normal_tail_forward")
+        ctx.keep = (d, a, m, rays)
+        ctx.shapes = (n01.shape, depth_img.shape)
+        return out[0], out[1]
+
+    @staticmethod
+    def backward(ctx, g_normal, g_ref):
+        d, a, m, rays = ctx.keep
+        H, W = (int(s) for s in d.shape)
+        gn = None if g_normal is None else _f32c(g_normal)
+        gr = None if g_ref is None else _f32c(g_ref)
+        g_n01 = torch.empty(3, H, W, dtype=torch.float32, device=d.device)
+        nd = 1
+        for s_ in ctx.shapes[1][:-2]:
+            nd *= int(s_)
+        g_depth = torch.zeros(nd, H, W, dtype=torch.float32, device=d.device) if nd > 1 else \
+            torch.empty(1, H, W, dtype=torch.float32, device=d.device)
+        with _nat.on_device(d.device):
+            rc = _nat.lib().r3dgw_normal_tail_backward(H, W, d.data_ptr(), a.data_ptr(), m.data_ptr(), rays.data_ptr(),
+                                                       None if gn is None else gn.data_ptr(),
+                                                       None if gr is None else gr.data_ptr(), g_n01.data_ptr(),
+                                                       g_depth.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_normal_tail_backward")
+        return g_n01.reshape(ctx.shapes[0]), g_depth.reshape(ctx.shapes[1]), None, None, None
+
+
+def normal_tail(view, n01_image, depth_image, alpha_image, sky_mask, rays=None):
+    """-> (normal [3,H,W], normal_ref [3,H,W]) exactly as render() composes them from the rasterized normal-colour
+    image (0.5 n + 0.5), the depth image (channel 0 is used), the alpha image (channel 0, treated as a constant like
+    the reference's .detach()) and the sky mask [H,W]."""
+    if rays is None:
+        rays = ray_basis(view)
+    return _NormalTailFn.apply(n01_image, depth_image, alpha_image, sky_mask, rays.detach())
+
+
+class _NormalLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, normal, normal_ref, occl, sky):
+        _require_cuda(normal, "normal_consistency_loss")
+        a, b = _f32c(normal), _f32c(normal_ref)
+        H, W = int(a.shape[-2]), int(a.shape[-1])
+        o = None if occl is None else _f32c(occl.reshape(-1, H, W)[0])
+        m = None if sky is None else _f32c(sky.reshape(-1, H, W)[0])
+        L = _nat.lib()
+        ws = torch.empty(L.r3dgw_image_loss_workspace_bytes(1, H, W), dtype=torch.uint8, device=a.device)
+        out = torch.empty(4, dtype=torch.float32, device=a.device)
+        with _nat.on_device(a.device):
+            rc = L.r3dgw_normal_loss_forward(H, W, a.data_ptr(), b.data_ptr(), None if o is None else o.data_ptr(),
+                                             None if m is None else m.data_ptr(), ws.data_ptr(), out.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_normal_loss_forward")
+        ctx.keep = (a, b, o, m)
+        ctx.shapes = (normal.shape, normal_ref.shape)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b, o, m = ctx.keep
+        H, W = int(a.shape[-2]), int(a.shape[-1])
+        coef = _f32c(g.reshape(1))
+        need_a, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        ga = torch.empty_like(a) if need_a else None
+        gb = torch.empty_like(b) if need_b else None
+        with _nat.on_device(a.device):
+            rc = _nat.lib().r3dgw_normal_loss_backward(H, W, a.data_ptr(), b.data_ptr(), None if o is None else o.data_ptr(),
+                                                       None if m is None else m.data_ptr(), coef.data_ptr(),
+                                                       None if ga is None else ga.data_ptr(),
+                                                       None if gb is None else gb.data_ptr(), _stream())
+        _nat.check(rc, "r3dgw_normal_loss_backward")
+        return (None if ga is None else ga.reshape(ctx.shapes[0]), None if gb is None else gb.reshape(ctx.shapes[1]),
+                None, None)
+
+
+def normal_consistency_loss(normal, normal_ref, occluders_mask=None, sky_mask=None):
+    """train.py:92-96 before the lambda: mean over pixels of 1 - sum_c (normal occl sky)_c (normal_ref occl sky)_c;
+    masks [H,W] / [1,H,W] (an expanded [3,H,W] view is read through its first channel)."""
+    return _NormalLossFn.apply(normal, normal_ref, occluders_mask, sky_mask)

@@ -32,7 +32,8 @@ SYMBOLS = [
     "r3dgw_envmap_resize_cubic", "r3dgw_envmap_sh_project", "r3dgw_sh_rotate_sweep", "r3dgw_envmap_sh_render",
     "r3dgw_preshade_forward", "r3dgw_preshade_backward", "r3dgw_gaussian_normal_forward",
     "r3dgw_gaussian_normal_backward", "r3dgw_gaussian_reg_workspace_bytes", "r3dgw_gaussian_regularisers_forward",
-    "r3dgw_gaussian_regularisers_backward",
+    "r3dgw_gaussian_regularisers_backward", "r3dgw_normal_tail_forward", "r3dgw_normal_tail_backward",
+    "r3dgw_normal_loss_forward", "r3dgw_normal_loss_backward",
 ]
 
 
@@ -175,6 +176,10 @@ def lib():
     L.r3dgw_ssim_l1_backward.argtypes = [ci, ci, ci, vp, vp, vp, sz, vp, vp, vp, vp, vp]
     L.r3dgw_masked_l1_forward.argtypes = [ci, ci, ci, vp, vp, vp, sz, ci, vp, vp, vp]
     L.r3dgw_masked_l1_backward.argtypes = [ci, ci, ci, vp, vp, vp, sz, ci, vp, vp, vp, vp]
+    L.r3dgw_normal_tail_forward.argtypes = [ci, ci] + [vp] * 8
+    L.r3dgw_normal_tail_backward.argtypes = [ci, ci] + [vp] * 9
+    L.r3dgw_normal_loss_forward.argtypes = [ci, ci] + [vp] * 7
+    L.r3dgw_normal_loss_backward.argtypes = [ci, ci] + [vp] * 8
     L.r3dgw_depth_to_normal_forward.argtypes = [ci, ci, vp, vp, vp, vp]
     L.r3dgw_depth_to_normal_backward.argtypes = [ci, ci, vp, vp, vp, vp, vp]
     cf = ctypes.c_float

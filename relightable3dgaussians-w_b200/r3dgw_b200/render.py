@@ -95,6 +95,14 @@ def _prepare(camera, pc, env_sh, sky_sh, shade_fn, specular, fix_sky):
     return colors, diffuse, spec, depth, 0.5 * normals + 0.5
 
 
+def image_post_ops_fused(out, camera, sky_mask, n01_image):
+    """The same tail as image_post_ops in ONE kernel (r3dgw_b200.image_ops.normal_tail): `n01_image` is the rasterized
+    normal-colour image before the (x - 0.5) * 2 step."""
+    from .image_ops import normal_tail
+    out["normal"], out["normal_ref"] = normal_tail(camera, n01_image, out["depth"], out["alpha"], sky_mask)
+    return out
+
+
 def image_post_ops(out, camera, sky_mask, depth_to_normal):
     """The image-space tail of the reference's render() (gaussian_renderer/__init__.py:233-237, 266-272), same torch
     expressions: the rendered normal composited over the sky, and `normal_ref` from the masked depth map.
@@ -150,14 +158,20 @@ def render(camera, pc, env_sh, sky_sh, raster, bg_color, shade_fn, scaling_modif
         sky_color[pc.is_sky] = colors[pc.is_sky]
         extras.update({"sky_color": sky_color, "roughness": rough_all.repeat(1, 3), "metalness": metal_all.repeat(1, 3),
                        "albedo": alb_all})
+    fuse_tail = sky_mask is not None and depth_to_normal is not None and getattr(depth_to_normal, "fused_tail", False)
+    n01_img = None
     for k, f in extras.items():
         img = call(rasterizer, f)[0]
         if k == "normal":
-            img = (img - 0.5) * 2.0
+            n01_img = img
+            if not fuse_tail:
+                img = (img - 0.5) * 2.0
         out[k] = img
     rasterizer_alpha = raster.GaussianRasterizer(raster_settings=settings(torch.zeros(3, device=means3D.device)))
     out["alpha"] = call(rasterizer_alpha, torch.ones_like(means3D))[0]
-    if sky_mask is not None and depth_to_normal is not None:
+    if fuse_tail:
+        image_post_ops_fused(out, camera, sky_mask, n01_img)
+    elif sky_mask is not None and depth_to_normal is not None:
         image_post_ops(out, camera, sky_mask, depth_to_normal)
     return out
 
@@ -189,7 +203,11 @@ def render_fused(camera, pc, env_sh, sky_sh, bg_color, shade_fn, scaling_modifie
                                                   pc.rotations, None, s, bg=bg16)
     out = {"render": img[0:3], "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii,
            "diffuse_color": img[3:6], "specular_color": img[6:9], "depth": img[9:12],
-           "normal": (img[12:15] - 0.5) * 2.0, "alpha": img[15:16].expand(3, -1, -1)}
+           "alpha": img[15:16].expand(3, -1, -1)}
+    if sky_mask is not None and depth_to_normal is not None and getattr(depth_to_normal, "fused_tail", False):
+        image_post_ops_fused(out, camera, sky_mask, img[12:15])
+        return out
+    out["normal"] = (img[12:15] - 0.5) * 2.0
     if sky_mask is not None and depth_to_normal is not None:
         image_post_ops(out, camera, sky_mask, depth_to_normal)
     return out

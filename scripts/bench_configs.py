@@ -172,7 +172,7 @@ def config_D(views, envmaps):
         dist.destroy_process_group()
 
 
-def config_E():
+def config_E(arms=("native", "reference")):
     import diff_gaussian_rasterization as dgr
     import ref_loader
     from r3dgw_b200.synthetic import make_scene
@@ -183,7 +183,7 @@ def config_E():
     dL = torch.full((3, H, W), 1e-3, device=dev)
     out = {"config": f"E: {sc.P} Gaussians at {W}x{H}, one raster call (U1), C = 3", "unit": "ms"}
     for tag, mod in (("native", dgr), ("reference", ref_loader.load_ref_dgr() if ref_loader.available() else None)):
-        if mod is None:
+        if mod is None or tag not in arms:
             continue
         s = mod.GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, sc.bg, 1.0, cam.world_view_transform,
                                               cam.full_proj_transform, -1, cam.camera_center, False)
@@ -217,5 +217,11 @@ if __name__ == "__main__":
     ap.add_argument("config", choices=["A", "D", "E"])
     ap.add_argument("--views", type=int, default=64)
     ap.add_argument("--envmaps", type=int, default=8)
+    ap.add_argument("--arm", default="both", choices=["both", "native", "reference"],
+                    help="config E: run one arm per process (the reference overflows its 32-bit buffer sizes at E and can "
+                         "leave the CUDA context in a failed state)")
     a = ap.parse_args()
-    {"A": config_A, "E": config_E}.get(a.config, lambda: config_D(a.views, a.envmaps))()
+    if a.config == "E":
+        config_E(("native", "reference") if a.arm == "both" else (a.arm,))
+    else:
+        {"A": config_A}.get(a.config, lambda: config_D(a.views, a.envmaps))()

@@ -229,3 +229,59 @@ def test_u2_training_step_native_vs_reference_arm(native_lib):
             noise = max(rel2(refs[i], refs[j]) for i in range(len(refs)) for j in range(i))
             bar = max(2e-3, 3.0 * noise)
             assert rel <= bar, f"{key} d_{nm}: relative L2 {rel:.3e} (bar {bar:.3e}, reference run-to-run {noise:.3e})"
+
+
+def test_fused_normal_tail_and_normal_loss_vs_reference_expressions(native_lib):
+    """normal_tail / normal_consistency_loss (one kernel each way) against the reference's chain of torch ops around the
+    pinned depth_to_normal kernel: gaussian_renderer/__init__.py:231-237, 266-271 and train.py:92-96."""
+    import math
+    from types import SimpleNamespace
+    from r3dgw_b200 import image_ops
+    from r3dgw_b200.synthetic import make_camera
+    dev = "cuda"
+    H, W = 270, 480
+    cam = make_camera(W, H).to(dev)
+    view = SimpleNamespace(world_view_transform=cam.world_view_transform, image_width=W, image_height=H, FoVx=cam.FoVx,
+                           FoVy=cam.FoVy)
+    g = torch.Generator().manual_seed(12)
+    yy, xx = torch.meshgrid(torch.linspace(0, 1, H), torch.linspace(0, 1, W), indexing="ij")
+    depth0 = (4.0 + 2.0 * torch.sin(6 * xx) * torch.cos(4 * yy) + 0.05 * torch.rand(H, W, generator=g))
+    base = {"n01": torch.rand(3, H, W, generator=g), "depth": depth0.unsqueeze(0).repeat(3, 1, 1).contiguous()}
+    alpha = torch.rand(3, H, W, generator=g).to(dev)
+    sky = torch.ones(H, W)
+    sky[: H // 5] = 0
+    sky[:, 100:140] = 0.5                      # a soft mask value exercises the products
+    sky = sky.to(dev)
+    occl = (torch.rand(1, H, W, generator=g) > 0.1).float().to(dev)
+    w_n = torch.randn(3, H, W, generator=g).to(dev)
+    w_r = torch.randn(3, H, W, generator=g).to(dev)
+
+    def leaves():
+        return {k: v.clone().to(dev).requires_grad_(True) for k, v in base.items()}
+
+    a = leaves()
+    normal, nref = image_ops.normal_tail(view, a["n01"], a["depth"], alpha, sky)
+    loss_a = image_ops.normal_consistency_loss(normal, nref, occl, sky)
+    ((normal * w_n).sum() + (nref * w_r).sum() + 3.0 * loss_a).backward()
+
+    b = leaves()
+    n = (b["n01"] - 0.5) * 2.0
+    n = n * sky + torch.ones_like(n) * (1 - sky)
+    r = image_ops.depth_to_normal(view, (b["depth"][0] * sky).unsqueeze(0)).permute(2, 0, 1)
+    r = r * alpha.detach()
+    r = r + torch.ones_like(r) * (1 - sky)
+    occl3, sky3 = occl.expand(3, H, W), sky.unsqueeze(0).expand(3, H, W)
+    rn, rs = n * occl3 * sky3, r * occl3 * sky3
+    loss_b = (1 - (rn * rs).sum(dim=0))[None].mean()
+    ((n * w_n).sum() + (r * w_r).sum() + 3.0 * loss_b).backward()
+
+    assert torch.equal(normal, n.detach()), (normal - n).abs().max().item()
+    assert (nref - r).abs().max().item() <= 1e-6
+    assert abs(float(loss_a) - float(loss_b)) <= 2e-6 * max(1.0, abs(float(loss_b)))
+    for k in base:
+        ga, gb = a[k].grad, b[k].grad
+        scale = gb.abs().max().item()
+        assert (ga - gb).abs().max().item() <= 1e-5 * scale + 1e-9, (k, (ga - gb).abs().max().item(), scale)
+    # bit-reproducible loss (fixed-order reduction)
+    assert torch.equal(image_ops.normal_consistency_loss(normal.detach(), nref.detach(), occl, sky),
+                       image_ops.normal_consistency_loss(normal.detach(), nref.detach(), occl, sky))
