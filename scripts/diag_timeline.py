@@ -9,7 +9,7 @@ dev = torch.device("cuda")
 sc, cam, gt = bench.build_workload("B", 0, dev)
 st = bench.Stepper("native", os.environ.get("DIAG_MODE", "dropin"), sc, cam, dev)
 gt = gt.cuda()
-for _ in range(15):
+for _ in range(int(os.environ.get("DIAG_WARM", "15"))):
     st.step(gt)
 torch.cuda.synchronize()
 gc.collect(); gc.disable()

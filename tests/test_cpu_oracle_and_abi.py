@@ -258,3 +258,24 @@ def test_envmap_api_surface_and_errors():
         E.get_coefficients_from_image(np.zeros((4, 8, 3), np.float32), 2)
     with pytest.raises(RuntimeError, match="no CPU path"):
         E.rotate_sh(np.zeros((3, 25)), 0.1, 0.2, 0.3)
+
+
+def test_allocation_holder_is_freed_by_refcount():
+    """The ctypes allocation callback must not keep its holder (and the state buffers it owns) alive in a reference
+    cycle: with the cyclic collector off - as it is inside timed / latency-critical loops - every frame's geometry and
+    binning buffers would otherwise pile up until the allocator runs dry."""
+    import gc
+    import weakref
+    import torch
+    import diff_gaussian_rasterization as dgr
+    gc.collect()
+    gc.disable()
+    try:
+        h = dgr._Holder(torch.device("cpu"), "test-role")
+        ptr = h.cb(None, 4096)
+        assert ptr and h.t is not None and h.t.numel() >= 4096
+        w = weakref.ref(h)
+        del h
+        assert w() is None
+    finally:
+        gc.enable()
