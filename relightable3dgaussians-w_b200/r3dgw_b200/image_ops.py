@@ -266,7 +266,8 @@ def normal_tail(view, n01_image, depth_image, alpha_image, sky_mask, rays=None):
     the reference's .detach()) and the sky mask [H,W]."""
     if rays is None:
         rays = ray_basis(view)
-    return _NormalTailFn.apply(n01_image, depth_image, alpha_image, sky_mask, rays.detach())
+    # .detach() as in the reference (`normal_ref * alpha.detach()`): the alpha raster call gets no backward pass
+    return _NormalTailFn.apply(n01_image, depth_image, alpha_image.detach(), sky_mask, rays.detach())
 
 
 class _NormalLossFn(torch.autograd.Function):
