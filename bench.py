@@ -382,6 +382,7 @@ def l2_flush(torch, buf):
 RANK0_SAMPLES = int(os.environ.get("RANK", "0")) == 0     # clocks are sampled by rank 0 only: 8 processes querying
 # NVML in the same step serialise in the driver (r01: 85-100 ms single-step stalls at N = 8)
 SAMPLE_EVERY_STEP = os.environ.get("R3DGW_BENCH_SAMPLE_EVERY", "0") == "1"      # diagnostics: clocks / reasons per step
+LAST_RANK_STATS = []   # per rank [mean step ms, max single step ms] of the most recent timed_steps() call (N > 1)
 LAST_STEP_MS = []      # per-step device times of the most recent timed_steps() call (diagnostics on stderr)
 
 
@@ -415,9 +416,15 @@ def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None, sampler=None):
     per_step = [a.elapsed_time(b) for a, b in evs]
     LAST_STEP_MS[:] = per_step
     total = sum(per_step)
+    LAST_RANK_STATS[:] = []
     if dist is not None:
         t = torch.tensor([total], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        # per-rank (mean, max single step): the reported time is the MAX over ranks, so one rank's hiccup shows here
+        mine = torch.tensor([total / max(steps, 1), max(per_step)], device="cuda", dtype=torch.float64)
+        allr = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+        dist.all_gather(allr, mine)
+        LAST_RANK_STATS[:] = [[round(float(x[0]), 3), round(float(x[1]), 3)] for x in allr]
         total = float(t.item())
     return total
 
@@ -519,7 +526,7 @@ def cpu_baseline(workload, budget_s=20.0):
     t_shade = time.perf_counter() - t0
     step_s = f * (6 * t_fwd + 5 * t_bwd + t_shade)
     ro.set_threads(1)
-    return {"value": 1.0 / step_s, "unit": UNIT, "cores": cores, "kind": "port",
+    return {"value": 1.0 / step_s, "unit": UNIT, "cores": cores, "kind": "port", "extrapolated": True,
             "sample": f"first {Ps} of {sc.P} Gaussians at {c.image_width}x{c.image_height}: 1 raster fwd {t_fwd:.2f}s + "
                       f"bwd {t_bwd:.2f}s (oracle/raster_oracle.c, OpenMP) + torch-CPU shading fwd+bwd {t_shade:.2f}s; "
                       f"extrapolated x{f} and to 6 fwd + 5 bwd per step",
@@ -633,8 +640,11 @@ def main():
                  "alloc_retries": int(ms1.get("num_alloc_retries", 0)),
                  "reserved_gb": round(ms1.get("reserved_bytes.all.current", 0) / 2**30, 2),
                  "peak_allocated_gb": round(ms1.get("allocated_bytes.all.peak", 0) / 2**30, 2)}
+    rank_stats = list(LAST_RANK_STATS)
     if rank == 0:
         print("step ms (resident):", [round(x, 2) for x in LAST_STEP_MS], file=sys.stderr)
+        if rank_stats:
+            print("per-rank [mean, max] step ms (resident):", rank_stats, file=sys.stderr)
         if SAMPLE_EVERY_STEP and sampler is not None:
             print("per-step (sm_mhz, power_w, reasons):", [(int(a), int(b), hex(c)) for a, b, c in sampler.samples], file=sys.stderr)
     clocks = sampler.summary() if sampler is not None else {"sm_mhz": None, "reasons": ["sampler disabled (R3DGW_BENCH_NO_SAMPLER=1)"]}
@@ -755,6 +765,7 @@ def main():
                        "caller": ("reference render() + train.py loss, unmodified (oracle/_ref/py)" if isinstance(st, StockStepper)
                                   else "r3dgw_b200.render (the repo's render() / render_fused(), reference call pattern)")},
             "clocks": clocks, "gpu_launches": int(gpu_launches), "allocator": allocator,
+            "per_rank_mean_max_step_ms": rank_stats,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": 4, "h2d_gbps_measured": round(h2d_gbps, 2),
                     "loss_read": "this step's loss is copied D2H right after its forward pass and read on the host "

@@ -355,14 +355,17 @@ int r3dgw_depth_to_normal_backward(int H, int W, const float* depth, const float
 
 /* image-space tail of render() (gaussian_renderer/__init__.py:231-237, 266-271), one kernel each way:
  *   normal     = ((n01 - 0.5) * 2) * sky + (1 - sky)            n01: rasterized 0.5 n + 0.5 image, f32[3,H,W]
- *   normal_ref = depth_to_normal(depth * sky) * alpha + (1 - sky)  depth / alpha: f32[H,W] (channel 0 of the images)
+ *   normal_ref = depth_to_normal(depth * sky) * alpha + (1 - sky)  depth: f32[H,W] (channel 0 of the depth image);
+ *                                                                  alpha: f32 planes at alpha_channel_stride elements
+ *                                                                  (H*W for a [3,H,W] image, 0 for one [H,W] plane)
  * rays: the 21 floats of r3dgw_depth_to_normal_*.  alpha is treated as a constant (the reference detaches it).
  * backward: any of dL_dnormal / dL_dnormal_ref may be NULL (zero); outputs dL_dn01 f32[3,H,W], dL_ddepth f32[H,W]. */
-int r3dgw_normal_tail_forward(int H, int W, const float* n01, const float* depth, const float* alpha, const float* sky,
-                              const float* rays, float* normal, float* normal_ref, void* stream);
-int r3dgw_normal_tail_backward(int H, int W, const float* depth, const float* alpha, const float* sky, const float* rays,
-                               const float* dL_dnormal, const float* dL_dnormal_ref, float* dL_dn01, float* dL_ddepth,
-                               void* stream);
+int r3dgw_normal_tail_forward(int H, int W, const float* n01, const float* depth, const float* alpha,
+                              size_t alpha_channel_stride, const float* sky, const float* rays, float* normal,
+                              float* normal_ref, void* stream);
+int r3dgw_normal_tail_backward(int H, int W, const float* depth, const float* alpha, size_t alpha_channel_stride,
+                               const float* sky, const float* rays, const float* dL_dnormal, const float* dL_dnormal_ref,
+                               float* dL_dn01, float* dL_ddepth, void* stream);
 /* normal-consistency term (train.py:92-96): out[0] = mean over the H*W pixels of
  * 1 - sum_c (normal_c occl sky)(normal_ref_c occl sky); occl / sky f32[H,W] or NULL (ones); fixed-order reduction.
  * workspace: r3dgw_image_loss_workspace_bytes(1,H,W).  backward: coef = device f32[1] upstream gradient. */

@@ -18,6 +18,7 @@
 // Every decision (power > 0, alpha < 1/255, T*(1-alpha) < 1e-4) is evaluated with the reference's
 // expression trees so that n_contrib is bit-identical and colours agree to rounding.
 #include <stdlib.h>
+#include <cstdlib>
 #include "common.cuh"
 #include "warp_reduce.cuh"
 
@@ -435,8 +436,8 @@ struct BwdSmem {
     uint64_t bar[2];
 };
 
-template <int C, int BATCH, bool COLOR, int QROWS>
-__global__ void __launch_bounds__(TILE_PIX) blend_backward_kernel(
+template <int C, int BATCH, bool COLOR, int QROWS, int MINB = 1>
+__global__ void __launch_bounds__(TILE_PIX, (MINB > 1 ? MINB : 0)) blend_backward_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatA, const float4* __restrict__ splatB,
     int W, int H, const float* __restrict__ bg_color, const float* __restrict__ features,
     const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
@@ -1078,16 +1079,16 @@ static int launch_forward(dim3 grid, const uint2* ranges, const float4* A, const
     return 0;
 }
 
-template <int C, int BATCH, bool COLOR, int QROWS = 0>
+template <int C, int BATCH, bool COLOR, int QROWS = 0, int MINB = 1>
 static int launch_backward(dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
                            const float* bg, const float* features, const float* final_T,
                            const uint32_t* n_contrib, const float* dL_dpix, float* dL_dmean2D,
                            float* dL_dconic, float* dL_dopacity, float* dL_dfeatures, cudaStream_t stream) {
     const int smem = (int)sizeof(BwdSmem<C, BATCH, COLOR, QROWS>);
-    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_kernel<C, BATCH, COLOR, QROWS>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_kernel<C, BATCH, COLOR, QROWS, MINB>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     {
         ProfScope ps(COLOR ? KID_BLEND_BWD : KID_BLEND_BWD_GEOM, stream);
-        blend_backward_kernel<C, BATCH, COLOR, QROWS><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
+        blend_backward_kernel<C, BATCH, COLOR, QROWS, MINB><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, bg, features, final_T, n_contrib,
                                                                                dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, dL_dfeatures);
     }
     R3DGW_LAUNCH_CHECK();
@@ -1116,6 +1117,11 @@ static int launch_backward_geom(dim3 grid, const uint2* ranges, const float4* A,
     // (66 KB of smem, 3 CTAs per SM); QROWS 16 / BATCH 64: 1.18 ms (41 KB, 4 CTAs); QROWS 8 / BATCH 64: 1.19 ms.
     // With COLOR = true the C colour sums still need their butterfly and the extra smem costs occupancy: no gain
     // (C = 3: 2.49 -> 2.59 ms fwd+bwd; C = 14: 2.46 -> 2.42 ms), so those kernels keep QROWS = 0.
+    if constexpr (C == 15 || C == 16) {      // occupancy experiment: R3DGW_BWDG_MINB=5 caps the kernel at 51 registers
+        static const int minb = [] { const char* e = getenv("R3DGW_BWDG_MINB"); return e ? atoi(e) : 1; }();
+        if (minb == 5)
+            return launch_backward<C, 64, false, 16, 5>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, nullptr, stream);
+    }
     return launch_backward<C, 64, false, 16>(grid, ranges, A, B, W, H, bg, features, final_T, n_contrib, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, nullptr, stream);
 }
 

@@ -416,7 +416,8 @@ __device__ __forceinline__ void normal_diffs_m(const float* __restrict__ depth, 
 
 __global__ void __launch_bounds__(256) normal_tail_forward_kernel(
     int H, int W, const float* __restrict__ n01, const float* __restrict__ depth, const float* __restrict__ alpha,
-    const float* __restrict__ sky, const float* __restrict__ rays, float* __restrict__ normal, float* __restrict__ normal_ref) {
+    size_t alpha_cstride, const float* __restrict__ sky, const float* __restrict__ rays, float* __restrict__ normal,
+    float* __restrict__ normal_ref) {
     __shared__ float M[RAYS_N];
     if (threadIdx.x < RAYS_N) M[threadIdx.x] = rays[threadIdx.x];
     __syncthreads();
@@ -432,28 +433,26 @@ __global__ void __launch_bounds__(256) normal_tail_forward_kernel(
         const float len = fmaxf(sqrtf(dot3(v, v)), 1e-12f);
         n = make_float3(v.x / len, v.y / len, v.z / len);
     }
-    const float a = alpha[i];
     const float nr[3] = {n.x, n.y, n.z};
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         const float v = __fmul_rn(__fsub_rn(n01[c * plane + i], 0.5f), 2.0f);
         normal[c * plane + i] = __fadd_rn(__fmul_rn(v, m), one_m);
-        normal_ref[c * plane + i] = __fadd_rn(__fmul_rn(nr[c], a), one_m);
+        normal_ref[c * plane + i] = __fadd_rn(__fmul_rn(nr[c], alpha[c * alpha_cstride + i]), one_m);
     }
 }
 
 // gradient of the (alpha-weighted) normal at interior pixel (cx, cy) w.r.t. its dx / dy vectors; g planar [3,H,W]
 __device__ __forceinline__ void normal_backprop_m(const float* __restrict__ depth, const float* __restrict__ sky,
                                                   const float* M, const float* __restrict__ g_ref,
-                                                  const float* __restrict__ alpha, int W, size_t plane, int cx, int cy,
-                                                  float3& g_dx, float3& g_dy) {
+                                                  const float* __restrict__ alpha, size_t acs, int W, size_t plane,
+                                                  int cx, int cy, float3& g_dx, float3& g_dy) {
     float3 dx, dy;
     normal_diffs_m(depth, sky, M, W, cx, cy, dx, dy);
     const float3 v = cross3(dx, dy);
     const float len = sqrtf(dot3(v, v));
     const size_t j = (size_t)cy * W + cx;
-    const float a = alpha[j];
-    const float3 g = make_float3(g_ref[j] * a, g_ref[plane + j] * a, g_ref[2 * plane + j] * a);
+    const float3 g = make_float3(g_ref[j] * alpha[j], g_ref[plane + j] * alpha[acs + j], g_ref[2 * plane + j] * alpha[2 * acs + j]);
     float3 u;
     if (len > 1e-12f) {
         const float inv = 1.f / len;
@@ -468,9 +467,9 @@ __device__ __forceinline__ void normal_backprop_m(const float* __restrict__ dept
 }
 
 __global__ void __launch_bounds__(256) normal_tail_backward_kernel(
-    int H, int W, const float* __restrict__ depth, const float* __restrict__ alpha, const float* __restrict__ sky,
-    const float* __restrict__ rays, const float* __restrict__ g_normal, const float* __restrict__ g_ref,
-    float* __restrict__ g_n01, float* __restrict__ g_depth) {
+    int H, int W, const float* __restrict__ depth, const float* __restrict__ alpha, size_t acs,
+    const float* __restrict__ sky, const float* __restrict__ rays, const float* __restrict__ g_normal,
+    const float* __restrict__ g_ref, float* __restrict__ g_n01, float* __restrict__ g_depth) {
     __shared__ float M[RAYS_N];
     if (threadIdx.x < RAYS_N) M[threadIdx.x] = rays[threadIdx.x];
     __syncthreads();
@@ -488,10 +487,10 @@ __global__ void __launch_bounds__(256) normal_tail_backward_kernel(
             const float3 r = ray_dir(M, x, y);
             float3 gdx, gdy;
             auto interior = [&](int cx, int cy) { return cx >= 1 && cx < W - 1 && cy >= 1 && cy < H - 1; };
-            if (interior(x, y - 1)) { normal_backprop_m(depth, sky, M, g_ref, alpha, W, plane, x, y - 1, gdx, gdy); acc += dot3(r, gdx); }
-            if (interior(x, y + 1)) { normal_backprop_m(depth, sky, M, g_ref, alpha, W, plane, x, y + 1, gdx, gdy); acc -= dot3(r, gdx); }
-            if (interior(x - 1, y)) { normal_backprop_m(depth, sky, M, g_ref, alpha, W, plane, x - 1, y, gdx, gdy); acc += dot3(r, gdy); }
-            if (interior(x + 1, y)) { normal_backprop_m(depth, sky, M, g_ref, alpha, W, plane, x + 1, y, gdx, gdy); acc -= dot3(r, gdy); }
+            if (interior(x, y - 1)) { normal_backprop_m(depth, sky, M, g_ref, alpha, acs, W, plane, x, y - 1, gdx, gdy); acc += dot3(r, gdx); }
+            if (interior(x, y + 1)) { normal_backprop_m(depth, sky, M, g_ref, alpha, acs, W, plane, x, y + 1, gdx, gdy); acc -= dot3(r, gdx); }
+            if (interior(x - 1, y)) { normal_backprop_m(depth, sky, M, g_ref, alpha, acs, W, plane, x - 1, y, gdx, gdy); acc += dot3(r, gdy); }
+            if (interior(x + 1, y)) { normal_backprop_m(depth, sky, M, g_ref, alpha, acs, W, plane, x + 1, y, gdx, gdy); acc -= dot3(r, gdy); }
         }
         g_depth[i] = acc * m;          // depth enters as depth * sky
     }
@@ -635,29 +634,31 @@ int r3dgw_masked_l1_backward(int C, int H, int W, const float* x, const float* t
     return 0;
 }
 
-int r3dgw_normal_tail_forward(int H, int W, const float* n01, const float* depth, const float* alpha, const float* sky,
-                              const float* rays, float* normal, float* normal_ref, void* stream_) {
+int r3dgw_normal_tail_forward(int H, int W, const float* n01, const float* depth, const float* alpha,
+                              size_t alpha_channel_stride, const float* sky, const float* rays, float* normal,
+                              float* normal_ref, void* stream_) {
     if (H <= 0 || W <= 0 || !n01 || !depth || !alpha || !sky || !rays || !normal || !normal_ref) return R3DGW_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
     dim3 grid((W + 31) / 32, (H + 7) / 8);
     {
         ProfScope ps(KID_DEPTH_NORMAL, stream);
-        normal_tail_forward_kernel<<<grid, 256, 0, stream>>>(H, W, n01, depth, alpha, sky, rays, normal, normal_ref);
+        normal_tail_forward_kernel<<<grid, 256, 0, stream>>>(H, W, n01, depth, alpha, alpha_channel_stride, sky, rays, normal,
+                                                             normal_ref);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;
 }
 
-int r3dgw_normal_tail_backward(int H, int W, const float* depth, const float* alpha, const float* sky, const float* rays,
-                               const float* dL_dnormal, const float* dL_dnormal_ref, float* dL_dn01, float* dL_ddepth,
-                               void* stream_) {
+int r3dgw_normal_tail_backward(int H, int W, const float* depth, const float* alpha, size_t alpha_channel_stride,
+                               const float* sky, const float* rays, const float* dL_dnormal, const float* dL_dnormal_ref,
+                               float* dL_dn01, float* dL_ddepth, void* stream_) {
     if (H <= 0 || W <= 0 || !depth || !alpha || !sky || !rays) return R3DGW_ERR_BAD_ARG;
     cudaStream_t stream = (cudaStream_t)stream_;
     dim3 grid((W + 31) / 32, (H + 7) / 8);
     {
         ProfScope ps(KID_DEPTH_NORMAL, stream);
-        normal_tail_backward_kernel<<<grid, 256, 0, stream>>>(H, W, depth, alpha, sky, rays, dL_dnormal, dL_dnormal_ref,
-                                                              dL_dn01, dL_ddepth);
+        normal_tail_backward_kernel<<<grid, 256, 0, stream>>>(H, W, depth, alpha, alpha_channel_stride, sky, rays, dL_dnormal,
+                                                              dL_dnormal_ref, dL_dn01, dL_ddepth);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;

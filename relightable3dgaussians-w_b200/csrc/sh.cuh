@@ -102,6 +102,62 @@ __host__ __device__ __forceinline__ void sh_basis_grad(float x, float y, float z
     }
 }
 
+// The same derivatives handed to a callback f(k, dYk/dx, dYk/dy, dYk/dz) one coefficient at a time, in index order:
+// a consumer that contracts them on the spot (sum_k c_k grad Y_k) keeps 3 accumulators instead of 3 (DEG+1)^2 values live.
+template <int DEG, class F>
+__host__ __device__ __forceinline__ void sh_basis_grad_each(float x, float y, float z, F&& f) {
+    f(0, 0.f, 0.f, 0.f);
+    if (DEG > 0) {
+        const float c1 = 0.4886025119029199f;
+        f(1, 0.f, -c1, 0.f);
+        f(2, 0.f, 0.f, c1);
+        f(3, -c1, 0.f, 0.f);
+    }
+    if (DEG > 1) {
+        const float a = 1.0925484305920792f, c6 = 0.31539156525252005f, c8 = 0.5462742152960396f;
+        f(4, a * y, a * x, 0.f);
+        f(5, 0.f, -a * z, -a * y);
+        f(6, -2.f * c6 * x, -2.f * c6 * y, 4.f * c6 * z);
+        f(7, -a * z, 0.f, -a * x);
+        f(8, 2.f * c8 * x, -2.f * c8 * y, 0.f);
+    }
+    float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+    if (DEG > 2) {
+        const float k9 = -0.5900435899266435f, k10 = 2.890611442640554f, k11 = -0.4570457994644658f,
+                    k12 = 0.3731763325901154f, k14 = 1.445305721320277f;
+        f(9, k9 * 6.f * xy, k9 * 3.f * (xx - yy), 0.f);
+        f(10, k10 * yz, k10 * xz, k10 * xy);
+        f(11, k11 * -2.f * xy, k11 * (4.f * zz - xx - 3.f * yy), k11 * 8.f * yz);
+        f(12, k12 * -6.f * xz, k12 * -6.f * yz, k12 * 3.f * (2.f * zz - xx - yy));
+        f(13, k11 * (4.f * zz - 3.f * xx - yy), k11 * -2.f * xy, k11 * 8.f * xz);
+        f(14, k14 * 2.f * xz, k14 * -2.f * yz, k14 * (xx - yy));
+        f(15, k9 * 3.f * (xx - yy), k9 * -6.f * xy, 0.f);
+    }
+    if (DEG > 3) {
+        const float k16 = 2.5033429417967046f, k17 = -1.7701307697799304f, k18 = 0.9461746957575601f,
+                    k19 = -0.6690465435572892f, k20 = 0.10578554691520431f, k22 = 0.47308734787878004f,
+                    k24 = 0.6258357354491761f;
+        // b16 = k16 (x^3 y - x y^3)
+        f(16, k16 * (3.f * xx * y - yy * y), k16 * (xx * x - 3.f * x * yy), 0.f);
+        // b17 = k17 (3 x^2 y z - y^3 z)
+        f(17, k17 * 6.f * xy * z, k17 * (3.f * xx - 3.f * yy) * z, k17 * y * (3.f * xx - yy));
+        // b18 = k18 xy (7 z^2 - 1)
+        f(18, k18 * y * (7.f * zz - 1.f), k18 * x * (7.f * zz - 1.f), k18 * 14.f * xy * z);
+        // b19 = k19 yz (7 z^2 - 3)
+        f(19, 0.f, k19 * z * (7.f * zz - 3.f), k19 * y * (21.f * zz - 3.f));
+        // b20 = k20 (35 z^4 - 30 z^2 + 3)
+        f(20, 0.f, 0.f, k20 * (140.f * zz * z - 60.f * z));
+        // b21 = k19 xz (7 z^2 - 3)
+        f(21, k19 * z * (7.f * zz - 3.f), 0.f, k19 * x * (21.f * zz - 3.f));
+        // b22 = k22 (x^2 - y^2)(7 z^2 - 1)
+        f(22, k22 * 2.f * x * (7.f * zz - 1.f), k22 * -2.f * y * (7.f * zz - 1.f), k22 * (xx - yy) * 14.f * z);
+        // b23 = k17 xz (x^2 - 3 y^2)
+        f(23, k17 * z * (3.f * xx - 3.f * yy), k17 * -6.f * xy * z, k17 * x * (xx - 3.f * yy));
+        // b24 = k24 (x^4 - 6 x^2 y^2 + y^4)
+        f(24, k24 * (4.f * xx * x - 12.f * x * yy), k24 * (4.f * yy * y - 12.f * xx * y), 0.f);
+    }
+}
+
 // d(v/|v|)/dv applied to a cotangent.  (same math as dnormvdv, cuda_rasterizer/auxiliary.h:107-118)
 __device__ __forceinline__ float3 normalize_bwd(float3 v, float3 g) {
     float s2 = v.x * v.x + v.y * v.y + v.z * v.z;

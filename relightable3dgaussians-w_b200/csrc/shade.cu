@@ -11,6 +11,7 @@
 //   (i+0.5)/256, clamp to edge - restated here; parity for it is unpinned by the reference.
 // One pass: 44 B in + 36 B out per Gaussian; the 25x3 environment SH and 4x3 sky SH live in shared
 // memory; the 512 KB FG LUT is served from L2.  HBM-bound streaming kernel.
+#include <cstdlib>
 #include "common.cuh"
 #include "sh.cuh"
 #include "warp_reduce.cuh"
@@ -253,8 +254,8 @@ __global__ void __launch_bounds__(256) shade_forward_kernel(const ShadeParams p,
 // Capping at 128 registers for 4 CTAs spills 544 B and is slower, 0.30 ms.)  Warps -> CTA through shared memory, one
 // atomicAdd per coefficient per CTA.
 constexpr int SHADE_BWD_THREADS = 128;
-template <int DEG, bool GEOM>
-__global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
+template <int DEG, bool GEOM, int MINB = 3>
+__global__ void __launch_bounds__(SHADE_BWD_THREADS, MINB) shade_backward_kernel(
     const ShadeParams p, const float* __restrict__ g_rgb, const float* __restrict__ g_dif,
     const float* __restrict__ g_spc, const float* __restrict__ g_depth3, const float* __restrict__ g_n01,
     float* __restrict__ d_pos, float* __restrict__ d_nrm, float* __restrict__ d_rot,
@@ -371,20 +372,25 @@ __global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
                 const float dfgy_du = u_in ? LUT_RES * ((1.f - t.fy) * (t01.y - t00.y) + t.fy * (t11.y - t10.y)) : 0.f;
                 const float dfgx_dv = v_in ? LUT_RES * ((1.f - t.fx) * (t10.x - t00.x) + t.fx * (t11.x - t01.x)) : 0.f;
                 const float dfgy_dv = v_in ? LUT_RES * ((1.f - t.fx) * (t10.y - t00.y) + t.fx * (t11.y - t01.y)) : 0.f;
-                float b[NSH], bx[NSH], by[NSH], bz[NSH];
+                // b[k] stays live; the 3 NSH basis derivatives are contracted one coefficient at a time by
+                // sh_basis_grad_each (the first version held b, bx, by, bz = 4 NSH values: 168 registers)
+                float b[NSH];
                 sh_basis<DEG>(r.x, r.y, r.z, b);
-                sh_basis_grad<DEG>(r.x, r.y, r.z, bx, by, bz);
                 float gl[DEG + 1], ggl[DEG + 1];
 #pragma unroll
                 for (int l = 0; l <= DEG; ++l) { gl[l] = expf(-(float)(l * (l + 1)) * (0.3f * kr)); ggl[l] = 0.f; }
                 float g_fgx = 0.f, g_fgy = 0.f;
-                float3 g_r = {0.f, 0.f, 0.f};
+                float si_raw[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+                for (int k = 0; k < NSH; ++k) {
+                    const float glk = gl[sh_band(k)];
+                    s_U[warp][k][lane] = b[k] * glk;
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) si_raw[c] += b[k] * (glk * s_env[3 * k + c]);
+                }
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
-                    float si_raw = 0.f;
-#pragma unroll
-                    for (int k = 0; k < NSH; ++k) si_raw += b[k] * (gl[sh_band(k)] * s_env[3 * k + c]);
-                    const float si = fmaxf(si_raw, 1e-4f);
+                    const float si = fmaxf(si_raw[c], 1e-4f);
                     const float F0 = has_km ? ((1.0f - km) * 0.04f + alb[c] * km) : 0.04f;
                     const float refl = F0 * fgx + fgy;
                     const float S = si * refl;
@@ -393,8 +399,7 @@ __global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
                     gD[c] = gdv[c] * gamma_bwd(D[c]) + one_m_km * g_sh;
                     const float gS = gsv[c] * gamma_bwd(S) + g_sh;
                     if (has_km) gkm += -D[c] * g_sh;
-                    const float g_si = (si_raw >= 1e-4f) ? gS * refl : 0.f;
-                    gs[c] = g_si;
+                    gs[c] = (si_raw[c] >= 1e-4f) ? gS * refl : 0.f;
                     const float g_refl = gS * si;
                     const float g_F0 = g_refl * fgx;
                     g_fgx += g_refl * F0;
@@ -403,17 +408,16 @@ __global__ void __launch_bounds__(SHADE_BWD_THREADS, 3) shade_backward_kernel(
                         galb[c] += g_F0 * km;
                         gkm += g_F0 * (alb[c] - 0.04f);
                     }
-#pragma unroll
-                    for (int k = 0; k < NSH; ++k) {
-                        const int l = sh_band(k);
-                        const float e = s_env[3 * k + c];
-                        ggl[l] += g_si * b[k] * e;
-                        const float ce = g_si * gl[l] * e;
-                        g_r.x += ce * bx[k]; g_r.y += ce * by[k]; g_r.z += ce * bz[k];
-                    }
                 }
-#pragma unroll
-                for (int k = 0; k < NSH; ++k) s_U[warp][k][lane] = b[k] * gl[sh_band(k)];
+                // w_k = sum_c g_si[c] env[k][c]:  d/d lobe_l += w_k b_k,  d/d r += w_k lobe_l grad Y_k
+                float3 g_r = {0.f, 0.f, 0.f};
+                sh_basis_grad_each<DEG>(r.x, r.y, r.z, [&](int k, float dbx, float dby, float dbz) {
+                    const float wk = gs[0] * s_env[3 * k] + gs[1] * s_env[3 * k + 1] + gs[2] * s_env[3 * k + 2];
+                    const int l = sh_band(k);
+                    ggl[l] += wk * b[k];
+                    const float cw = wk * gl[l];
+                    g_r.x += cw * dbx; g_r.y += cw * dby; g_r.z += cw * dbz;
+                });
                 any_spec = true;
 #pragma unroll
                 for (int l = 1; l <= DEG; ++l) gkr += ggl[l] * (-0.3f * (float)(l * (l + 1))) * gl[l];
@@ -562,10 +566,16 @@ static int launch_shade_backward(const ShadeParams& p, const float* g_rgb, const
     ProfScope ps(KID_SHADE_BWD, stream);
 #define R3DGW_SHADE_BWD(D) shade_backward_kernel<D, GEOM><<<blocks, SHADE_BWD_THREADS, 0, stream>>>( \
         p, g_rgb, g_dif, g_spc, g_depth3, g_n01, d_pos, d_nrm, d_rot, d_alb, d_kr, d_km, d_env, d_sky)
+    static const int minb = [] { const char* e = getenv("R3DGW_SHADE_BWD_MINB"); return e ? atoi(e) : 3; }();
     switch (p.sh_degree) {
         case 2: R3DGW_SHADE_BWD(2); break;
         case 3: R3DGW_SHADE_BWD(3); break;
-        default: R3DGW_SHADE_BWD(4); break;
+        default:
+            if (minb == 4)      // occupancy experiment: 128 registers / 4 CTAs per SM instead of 168 / 3
+                shade_backward_kernel<4, GEOM, 4><<<blocks, SHADE_BWD_THREADS, 0, stream>>>(
+                    p, g_rgb, g_dif, g_spc, g_depth3, g_n01, d_pos, d_nrm, d_rot, d_alb, d_kr, d_km, d_env, d_sky);
+            else R3DGW_SHADE_BWD(4);
+            break;
     }
 #undef R3DGW_SHADE_BWD
     R3DGW_LAUNCH_CHECK();

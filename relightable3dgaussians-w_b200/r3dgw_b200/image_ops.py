@@ -228,14 +228,19 @@ class _NormalTailFn(torch.autograd.Function):
         n = _f32c(n01)
         H, W = int(n.shape[-2]), int(n.shape[-1])
         d = _f32c(depth_img.reshape(-1, H, W)[0])
-        a = _f32c(alpha_img.reshape(-1, H, W)[0])
+        al = alpha_img.reshape(-1, H, W)
+        if al.shape[0] == 1 or al.stride(0) == 0:        # one plane (or an expanded view of one): read it for all channels
+            a, acs = _f32c(al[0]), 0
+        else:
+            a, acs = _f32c(al[:3]), H * W
         m = _f32c(sky.reshape(H, W))
         out = torch.empty(2, 3, H, W, dtype=torch.float32, device=n.device)
         with _nat.on_device(n.device):
-            rc = _nat.lib().r3dgw_normal_tail_forward(H, W, n.data_ptr(), d.data_ptr(), a.data_ptr(), m.data_ptr(),
+            rc = _nat.lib().r3dgw_normal_tail_forward(H, W, n.data_ptr(), d.data_ptr(), a.data_ptr(), acs, m.data_ptr(),
                                                       rays.data_ptr(), out[0].data_ptr(), out[1].data_ptr(), _stream())
         _nat.check(rc, "r3dgw_normal_tail_forward")
         ctx.keep = (d, a, m, rays)
+        ctx.acs = acs
         ctx.shapes = (n01.shape, depth_img.shape)
         return out[0], out[1]
 
@@ -252,7 +257,7 @@ class _NormalTailFn(torch.autograd.Function):
         g_depth = torch.zeros(nd, H, W, dtype=torch.float32, device=d.device) if nd > 1 else \
             torch.empty(1, H, W, dtype=torch.float32, device=d.device)
         with _nat.on_device(d.device):
-            rc = _nat.lib().r3dgw_normal_tail_backward(H, W, d.data_ptr(), a.data_ptr(), m.data_ptr(), rays.data_ptr(),
+            rc = _nat.lib().r3dgw_normal_tail_backward(H, W, d.data_ptr(), a.data_ptr(), ctx.acs, m.data_ptr(), rays.data_ptr(),
                                                        None if gn is None else gn.data_ptr(),
                                                        None if gr is None else gr.data_ptr(), g_n01.data_ptr(),
                                                        g_depth.data_ptr(), _stream())

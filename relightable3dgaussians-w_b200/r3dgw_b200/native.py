@@ -176,8 +176,8 @@ def lib():
     L.r3dgw_ssim_l1_backward.argtypes = [ci, ci, ci, vp, vp, vp, sz, vp, vp, vp, vp, vp]
     L.r3dgw_masked_l1_forward.argtypes = [ci, ci, ci, vp, vp, vp, sz, ci, vp, vp, vp]
     L.r3dgw_masked_l1_backward.argtypes = [ci, ci, ci, vp, vp, vp, sz, ci, vp, vp, vp, vp]
-    L.r3dgw_normal_tail_forward.argtypes = [ci, ci] + [vp] * 8
-    L.r3dgw_normal_tail_backward.argtypes = [ci, ci] + [vp] * 9
+    L.r3dgw_normal_tail_forward.argtypes = [ci, ci, vp, vp, vp, ctypes.c_size_t, vp, vp, vp, vp, vp]
+    L.r3dgw_normal_tail_backward.argtypes = [ci, ci, vp, vp, ctypes.c_size_t, vp, vp, vp, vp, vp, vp, vp]
     L.r3dgw_normal_loss_forward.argtypes = [ci, ci] + [vp] * 7
     L.r3dgw_normal_loss_backward.argtypes = [ci, ci] + [vp] * 8
     L.r3dgw_depth_to_normal_forward.argtypes = [ci, ci, vp, vp, vp, vp]
