@@ -7,7 +7,7 @@ import bench
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 mode = sys.argv[2] if len(sys.argv) > 2 else "dropin"
 sc, cam, gt = bench.build_workload("B", 0, torch.device("cuda"))
-st = bench.Stepper("native", mode, sc, cam, torch.device("cuda"))
+st = bench.make_stepper("native", mode, sc, cam, torch.device("cuda"))
 gt = gt.cuda()
 for _ in range(steps):
     st.step(gt)
