@@ -918,7 +918,7 @@ def main():
         traffic = None       # dram__bytes_read+write per launch from the committed `ncu --set full` capture (C = 3, config B)
         try:
             if args.workload == "B":
-                traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))[top]["dram_traffic_bytes_per_launch"]
+                traffic = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))[top]["dram_traffic_bytes_per_launch"]
         except Exception:   # noqa: BLE001
             pass
         # SURVEY 8(d)'s closed forms for the REFERENCE algorithm's compulsory bytes of the same stage: a replay kernel reads

@@ -557,6 +557,7 @@ def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, mean
     prev = _cache["entry"]
     if prev is not None:
         _alpha_pool["prev_calls"] = prev[0].blend_calls
+        prev[0].pending.clear()      # a backward pass that aborted half-way must not keep its tensors alive
     box = []
     handles = _GeometryFn.apply(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, box, means2D)
     st = box[0]

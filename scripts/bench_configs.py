@@ -118,7 +118,7 @@ def config_A():
     print(json.dumps(out))
 
 
-def config_D(views, envmaps):
+def config_D(views, envmaps, mode="dropin"):
     from r3dgw_b200.parallel import grid_cells_for_rank
     from r3dgw_b200.synthetic import CONFIGS, arc_cameras, make_env_sh, make_scene
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
@@ -133,7 +133,7 @@ def config_D(views, envmaps):
     cfg = CONFIGS["B"]
     cams = [c.to(dev) for c in arc_cameras(cfg["W"], cfg["H"], views, centroid_z=8.0, step_deg=1.0)]
     envs = make_env_sh(torch.Generator().manual_seed(20261104 + 3), envmaps).to(dev)       # seeds +0..+7 of config 4
-    st = bench.make_stepper("native", "dropin", sc, cams[0], dev)
+    st = bench.make_stepper("native", mode, sc, cams[0], dev)
     cells = grid_cells_for_rank(views, envmaps, rank, world)
     sink = torch.zeros((), device=dev)
 
@@ -163,7 +163,7 @@ def config_D(views, envmaps):
     if rank == 0:
         import diff_gaussian_rasterization as dgr
         print(json.dumps({"config": f"D: 1000000 Gaussians x {envmaps} envmaps x {views} views at 1920x1080, view-major "
-                                    f"cells over {world} rank(s), render() forward, geometry reused across the envmaps of a view",
+                                    f"cells over {world} rank(s), {'render_fused()' if mode == 'fused' else 'render()'} forward, geometry reused across the envmaps of a view",
                           "metric": "relit_eval_cells_per_s", "value": views * envmaps / (ms * 1e-3), "unit": "cells/s",
                           "n_gpus": world, "ms_per_grid": ms, "cells": views * envmaps, "scaling": "strong",
                           "stats_last_grid": dgr.stats()}))
@@ -217,6 +217,7 @@ if __name__ == "__main__":
     ap.add_argument("config", choices=["A", "D", "E"])
     ap.add_argument("--views", type=int, default=64)
     ap.add_argument("--envmaps", type=int, default=8)
+    ap.add_argument("--mode", default="dropin", choices=["dropin", "fused"], help="config D: render() or render_fused()")
     ap.add_argument("--arm", default="both", choices=["both", "native", "reference"],
                     help="config E: run one arm per process (the reference overflows its 32-bit buffer sizes at E and can "
                          "leave the CUDA context in a failed state)")
@@ -224,4 +225,4 @@ if __name__ == "__main__":
     if a.config == "E":
         config_E(("native", "reference") if a.arm == "both" else (a.arm,))
     else:
-        {"A": config_A}.get(a.config, lambda: config_D(a.views, a.envmaps))()
+        {"A": config_A}.get(a.config, lambda: config_D(a.views, a.envmaps, a.mode))()

@@ -94,7 +94,7 @@ def test_gradients_vs_fp64_evaluation_of_the_reference_backward(mods, name, n_ca
     truth = f64.backward_f64(rb, sc.means3D, sc.scales, sc.rotations, list(zip(feats, bgs, dLs)), sc.camera, radii)
 
     g_ref, c_ref = _run(ref, sc, feats, bgs, dLs)
-    dgr.set_alpha_cache(True)
+    dgr.clear_geometry_cache()
     g_new, c_new = _run(dgr, sc, feats, bgs, dLs)
     report = [f"config {name}, {n_calls} raster call(s), P={P} R={R}"]
     bad = []

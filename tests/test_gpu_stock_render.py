@@ -49,6 +49,31 @@ def _view(sc_, scene, dev, seed=3):
     return sc_.make_view(cam, sky, occl, gt)
 
 
+def _fresh(dgr):
+    """forget the geometry / blend history of earlier tests in this process (keeps the env switches as they are)"""
+    dgr.clear_geometry_cache()
+    dgr._alpha_pool["prev_calls"] = 0
+    dgr.reset_stats()
+
+
+def _expect_forward(dgr, st, calls, first_frame):
+    assert st["geometry_builds"] == 1 and st["geometry_hits"] == calls - 1, st
+    assert st["blend_plain"] + st["blend_record"] + st["blend_replay"] == calls, st
+    if not dgr._ALPHA_CACHE:            # R3DGW_ALPHA_CACHE=0: one plain K4 per call
+        assert st["blend_plain"] == calls, st
+    elif first_frame:                   # plain, record, then replays
+        assert st["blend_record"] == 1 and st["blend_replay"] == calls - 2, st
+    else:                               # a render() loop: the first blend already records
+        assert st["blend_record"] == 1 and st["blend_replay"] == calls - 1, st
+
+
+def _expect_backward(dgr, st, n_bwd):
+    if dgr._ALPHA_CACHE and dgr._DEFER_BWD:
+        assert st["backward_color_only"] == n_bwd and st["backward_geometry_only"] == 1 and st["backward_full"] == 0, st
+    else:                               # R3DGW_DEFERRED_BACKWARD=0 / no cache: one full K5 per call
+        assert st["backward_full"] == n_bwd and st["backward_color_only"] == 0, st
+
+
 def _close_img(a, b, name, tol):
     err = (a.detach() - b.detach()).abs().max().item()
     assert err <= tol, f"{name}: max abs err {err:.3e} > {tol}"
@@ -84,22 +109,17 @@ def test_stock_render_runs_unchanged_on_the_dropins(native_lib):
         else:
             env = EnvironmentLight(env_base, 4, fg_lut=lut)
             renderer = r_new
-            dgr.set_alpha_cache(True)       # also forgets the blend history of earlier tests in this process
-            dgr.reset_stats()
+            _fresh(dgr)
         pkg = sc_.stock_render(renderer, view, gm, env, sky, bg, debug=False)
         if arm == "new":
-            st = dgr.stats()
-            assert st["geometry_builds"] == 1 and st["geometry_hits"] == 5, st
-            assert st["blend_plain"] + st["blend_record"] + st["blend_replay"] == 6, st
-            assert st["blend_record"] == 1 and st["blend_replay"] >= 4, st
+            _expect_forward(dgr, dgr.stats(), 6, first_frame=True)
         g = torch.Generator().manual_seed(11)
         loss = 0.0
         for k in ("render", "diffuse_color", "specular_color", "depth", "normal", "normal_ref"):
             loss = loss + (pkg[k] * torch.randn(pkg[k].shape, generator=g).to(dev)).sum() * 1e-3
         loss.backward()
         if arm == "new":
-            st = dgr.stats()
-            assert st["backward_color_only"] == 5 and st["backward_geometry_only"] == 1 and st["backward_full"] == 0, st
+            _expect_backward(dgr, dgr.stats(), 5)
         outs[arm] = pkg
         leaves = sc_.model_leaves(gm) + [env_base, sky]
         grads[arm] = [None if p.grad is None else p.grad.detach().clone() for p in leaves] + \
@@ -146,7 +166,7 @@ def test_second_frame_records_on_first_blend_and_loss_matches(native_lib):
         env_base = scene.env_sh.to(dev).clone().requires_grad_(True)
         sky = scene.sky_sh.to(dev).reshape(1, 4, 3).clone().requires_grad_(True)
         env = sc_.make_ref_envlight(env_base, 4) if arm == "ref" else EnvironmentLight(env_base, 4, fg_lut=lut)
-        dgr.set_alpha_cache(True)
+        _fresh(dgr)
         for it in range(2):
             with torch.no_grad():                     # an optimizer-style in-place update between the frames
                 for p in sc_.model_leaves(gm):
@@ -157,10 +177,8 @@ def test_second_frame_records_on_first_blend_and_loss_matches(native_lib):
             loss = sc_.train_loss(pkg, view, gm, fns, LAM)
             loss.backward()
             if arm == "new":
-                st = dgr.stats()
-                assert st["geometry_builds"] == 1 and st["geometry_hits"] == 5, st
-                if it == 1:
-                    assert st["blend_record"] == 1 and st["blend_replay"] == 5, st
+                _expect_forward(dgr, dgr.stats(), 6, first_frame=(it == 0))
+                _expect_backward(dgr, dgr.stats(), 5)
         vals[arm] = (float(loss), [p.grad.detach().clone() for p in sc_.model_leaves(gm)[:4]])
     assert abs(vals["ref"][0] - vals["new"][0]) <= 2e-5 * abs(vals["ref"][0]), vals
     for nm, ga, gb in zip(("xyz", "scaling", "rotation", "opacity"), vals["ref"][1], vals["new"][1]):
@@ -178,8 +196,7 @@ def test_debug_render_keys_and_images(native_lib):
         gm = sc_.make_ref_model(scene, dev, requires_grad=False)
         sky = scene.sky_sh.to(dev).reshape(1, 4, 3)
         a = sc_.stock_render(r_ref, view, gm, sc_.make_ref_envlight(scene.env_sh.to(dev), 4), sky, bg, debug=True)
-        dgr.clear_geometry_cache()
-        dgr.reset_stats()
+        _fresh(dgr)
         b = sc_.stock_render(r_new, view, gm, EnvironmentLight(scene.env_sh.to(dev), 4, fg_lut=lut), sky, bg, debug=True)
     st = dgr.stats()
     assert st["geometry_builds"] == 1 and st["geometry_hits"] == 9, st       # 10 raster calls in debug mode
