@@ -174,8 +174,8 @@ class Stepper:
         if impl == "native":
             import diff_gaussian_rasterization as dgr
             from r3dgw_b200 import image_ops
-            from r3dgw_b200.regularisers import gaussian_regularisers
-            self.reg = gaussian_regularisers
+            from r3dgw_b200.losses import training_loss
+            self.train_loss = training_loss
             self.raster = dgr
             self.shade_fn = R.fused_shade_fn(self.lut, 4)
             self.ops = image_ops
@@ -221,31 +221,23 @@ class Stepper:
         planar-scale and sky-depth regularisers (the env-SH positivity term, train.py:99-102, samples 10 random
         directions on a [10,25,3] tensor - negligible and stochastic - and is left out of both arms)."""
         torch, ops, pc = self.torch, self.ops, self.pc
+        if self.impl == "native":
+            # the whole loss as ONE autograd node over the fused kernels (r3dgw_b200.losses): same terms, same kernels
+            # as the separate drop-ins, without ~8 Function calls and ~25 scalar torch kernels per step
+            return self.train_loss(out, gt, occl1, sky2, pc.scales, pc.means3D, pc.sky_index()[0],
+                                   cam.world_view_transform, LAMBDA)[0]
         gt3 = gt
         occl3, sky3 = occl1.expand_as(gt3), sky2.unsqueeze(0).expand_as(gt3)
-        if self.mode == "fused" and self.impl == "native":
-            loss = ops.photometric_loss(out["render"], gt3, occl3, LAMBDA["dssim"])[0]
-            loss_sky = ops.l1_loss(out["diffuse_color"], None, mask=sky2, complement_mask=True) + \
-                ops.l1_loss(out["specular_color"], None, mask=sky2, complement_mask=True)
-        else:
-            Ll1 = ops.l1_loss(out["render"], gt3, mask=occl3)
-            Ssim = 1.0 - ops.ssim(out["render"], gt3, mask=occl3)
-            loss = Ll1 * (1 - LAMBDA["dssim"]) + LAMBDA["dssim"] * Ssim
-            loss_sky = ops.l1_loss(out["diffuse_color"], torch.zeros_like(out["diffuse_color"]), mask=1 - sky3) + \
-                ops.l1_loss(out["specular_color"], torch.zeros_like(out["specular_color"]), mask=1 - sky3)
+        Ll1 = ops.l1_loss(out["render"], gt3, mask=occl3)
+        Ssim = 1.0 - ops.ssim(out["render"], gt3, mask=occl3)
+        loss = Ll1 * (1 - LAMBDA["dssim"]) + LAMBDA["dssim"] * Ssim
+        loss_sky = ops.l1_loss(out["diffuse_color"], torch.zeros_like(out["diffuse_color"]), mask=1 - sky3) + \
+            ops.l1_loss(out["specular_color"], torch.zeros_like(out["specular_color"]), mask=1 - sky3)
         loss = loss + LAMBDA["sky_brdf"] * loss_sky
-        if self.impl == "native":
-            loss = loss + LAMBDA["normal"] * ops.normal_consistency_loss(out["normal"], out["normal_ref"], occl1, sky2)
-        else:
-            rn = out["normal"] * occl3 * sky3
-            rs = out["normal_ref"] * occl3 * sky3
-            loss = loss + LAMBDA["normal"] * (1 - (rn * rs).sum(dim=0))[None].mean()
+        rn = out["normal"] * occl3 * sky3
+        rs = out["normal_ref"] * occl3 * sky3
+        loss = loss + LAMBDA["normal"] * (1 - (rn * rs).sum(dim=0))[None].mean()
         # min_scale_loss (utils/loss_utils.py:210-220) and depth_loss_gaussians (:140-148)
-        if self.impl == "native":
-            # one masked fixed-order reduction each way, no boolean-mask gathers / sort / host syncs (SURVEY 8f N1)
-            l_scale, l_depth, _ = self.reg(pc.scales, pc.means3D, out["radii"], pc.sky_index()[0],
-                                           cam.world_view_transform, 0.02)
-            return loss + LAMBDA["scale"] * l_scale + LAMBDA["sky_gauss"] * l_depth
         # the reference's caller-side torch on [P] arrays
         vis = out["radii"] > 0
         is_sky = pc.is_sky.reshape(-1)

@@ -285,3 +285,58 @@ def test_fused_normal_tail_and_normal_loss_vs_reference_expressions(native_lib):
     # bit-reproducible loss (fixed-order reduction)
     assert torch.equal(image_ops.normal_consistency_loss(normal.detach(), nref.detach(), occl, sky),
                        image_ops.normal_consistency_loss(normal.detach(), nref.detach(), occl, sky))
+
+
+def test_training_loss_node_equals_the_separate_dropins(native_lib):
+    """r3dgw_b200.losses.training_loss (one autograd node) against the sum of the separately pinned drop-ins
+    (l1_loss, ssim, normal_consistency_loss, min_scale_loss / depth_loss_gaussians) with train.py's lambdas."""
+    from types import SimpleNamespace
+    from r3dgw_b200 import image_ops, regularisers
+    from r3dgw_b200.losses import training_loss
+    dev = "cuda"
+    H, W, P = 135, 240, 5000
+    g = torch.Generator().manual_seed(21)
+    lam = {"dssim": 0.2, "sky_brdf": 0.5, "normal": 0.05, "scale": 100.0, "sky_gauss": 0.05}
+    base = {k: torch.rand(3, H, W, generator=g) for k in ("render", "diffuse_color", "specular_color")}
+    base["normal"] = torch.randn(3, H, W, generator=g)
+    base["normal_ref"] = torch.randn(3, H, W, generator=g)
+    base["scales"] = torch.rand(P, 3, generator=g) * 0.1 + 0.01
+    base["means3D"] = torch.randn(P, 3, generator=g) * 3 + torch.tensor([0.0, 0.0, 8.0])
+    gt = torch.rand(3, H, W, generator=g).to(dev)
+    occl = (torch.rand(1, H, W, generator=g) > 0.1).float().to(dev)
+    sky = torch.ones(H, W)
+    sky[: H // 5] = 0
+    sky = sky.to(dev)
+    radii = ((torch.rand(P, generator=g) < 0.7).int() * 5).to(dev)
+    is_sky = (torch.rand(P, generator=g) < 0.1).to(dev)
+    wvt = torch.eye(4, device=dev)
+    wvt[3, 2] = 0.5
+
+    def leaves():
+        return {k: v.clone().to(dev).requires_grad_(True) for k, v in base.items()}
+
+    a = leaves()
+    pkg = {k: a[k] for k in ("render", "diffuse_color", "specular_color", "normal", "normal_ref")}
+    pkg["radii"] = radii
+    loss_a, parts = training_loss(pkg, gt, occl, sky, a["scales"], a["means3D"], is_sky, wvt, lam)
+    (loss_a * 1.7).backward()
+
+    b = leaves()
+    occl3, sky3 = occl.expand(3, H, W), sky.unsqueeze(0).expand(3, H, W)
+    l1 = image_ops.l1_loss(b["render"], gt, mask=occl3)
+    ss = 1.0 - image_ops.ssim(b["render"], gt, mask=occl3)
+    loss_b = l1 * (1 - lam["dssim"]) + lam["dssim"] * ss
+    loss_b = loss_b + lam["sky_brdf"] * (image_ops.l1_loss(b["diffuse_color"], torch.zeros_like(b["diffuse_color"]), mask=1 - sky3)
+                                         + image_ops.l1_loss(b["specular_color"], torch.zeros_like(b["specular_color"]), mask=1 - sky3))
+    loss_b = loss_b + lam["normal"] * image_ops.normal_consistency_loss(b["normal"], b["normal_ref"], occl, sky)
+    ls, ld, _ = regularisers.gaussian_regularisers(b["scales"], b["means3D"], radii, is_sky, wvt, 0.02)
+    loss_b = loss_b + lam["scale"] * ls + lam["sky_gauss"] * ld
+    (loss_b * 1.7).backward()
+
+    assert abs(float(loss_a) - float(loss_b)) <= 2e-6 * abs(float(loss_b)), (float(loss_a), float(loss_b))
+    assert abs(float(parts[1]) - float(l1)) <= 1e-7 and abs(float(parts[16]) - float(ls)) <= 1e-7
+    for k in base:
+        ga, gb = a[k].grad, b[k].grad
+        assert ga is not None and gb is not None, k
+        scale = gb.abs().max().item()
+        assert (ga - gb).abs().max().item() <= 2e-6 * scale + 1e-12, (k, (ga - gb).abs().max().item(), scale)
