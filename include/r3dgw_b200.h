@@ -186,6 +186,17 @@ int r3dgw_blend_backward_color_cached(
                                 * (warp, Gaussian) pair leave as ONE 16-byte reduction instead of C 4-byte ones) */
     void* stream);
 
+/* Geometry gradients (dL/dmean2D [P,3], dL/dconic [P,4], dL/dopacity [P]; ACCUMULATED, zero them first) of one or
+ * several blends over one geometry, from the alpha cache, walking FRONT TO BACK: the reference's suffix sums
+ * (backward.cu:464-520) are the pixel's <forward output, dL/dpixel> minus a running prefix, so no conic / exp / T
+ * division is re-evaluated.  features f32[P,C], out_images f32[C,H,W] = the forward outputs of those blends
+ * (background included), background f32[C], dL_dpixels f32[C,H,W]; C in {3,4,6,8,9,12,15,16} (several calls
+ * concatenated along C). */
+int r3dgw_blend_backward_geometry_cached(int P, int R, int C, const r3dgw_camera* cam, const char* binning_buffer,
+                                         const char* image_buffer, const float* alpha_cache, const float* features,
+                                         const float* out_images, const float* background, const float* dL_dpixels,
+                                         float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, void* stream);
+
 /* K6+K7 fused: conic/mean2D gradients -> means3D, cov3D, scales, rotations (and SH).
  * Overwrites dL_dmean3D/dL_dcov3D/dL_dscale/dL_drot rows of visible Gaussians (caller zeroes).
  * Reference: BACKWARD::preprocess, backward.cu:144-396, 560-624. */

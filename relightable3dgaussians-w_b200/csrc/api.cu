@@ -57,6 +57,11 @@ int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4*
 int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
                                          const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
                                          float* dL_dfeatures, int grad_stride, cudaStream_t stream);
+int blend_backward_geometry_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W,
+                                            int H, const float* features, const uint32_t* n_contrib,
+                                            const float* alpha_cache, const float* out_images, const float* bg,
+                                            const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                                            cudaStream_t stream);
 int sort_num_passes(int end_bit);
 
 static inline int pre_blocks(int P) { return (P + PRE_THREADS - 1) / PRE_THREADS; }
@@ -362,6 +367,26 @@ int r3dgw_blend_backward_color_cached(int P, int R, int C, const r3dgw_camera* c
     return blend_backward_color_cached_dispatch(C, grid, (const uint2*)(binning_buffer + BL.ranges), A + R, W, H,
                                                 (const uint32_t*)(image_buffer + IL.n_contrib), alpha_cache,
                                                 dL_dpixels, dL_dfeatures, grad_stride, stream);
+}
+
+int r3dgw_blend_backward_geometry_cached(int P, int R, int C, const r3dgw_camera* cam, const char* binning_buffer,
+                                         const char* image_buffer, const float* alpha_cache, const float* features,
+                                         const float* out_images, const float* background, const float* dL_dpixels,
+                                         float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, void* stream_) {
+    if (!cam || !binning_buffer || !image_buffer || !features || !out_images || !background || !dL_dpixels || !dL_dmean2D || !dL_dconic ||
+        !dL_dopacity || R < 0 || P < 0)
+        return R3DGW_ERR_BAD_ARG;
+    if (R == 0) return 0;
+    if (!alpha_cache) return R3DGW_ERR_BAD_ARG;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int W = cam->width, H = cam->height;
+    r3dgw_binning_layout BL; binning_layout(R, W, H, &BL);
+    r3dgw_image_layout IL; image_layout(W, H, &IL);
+    dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
+    const float4* A = (const float4*)(binning_buffer + BL.splats);
+    return blend_backward_geometry_cached_dispatch(C, grid, (const uint2*)(binning_buffer + BL.ranges), A, A + R, W, H, features,
+                                                   (const uint32_t*)(image_buffer + IL.n_contrib), alpha_cache, out_images,
+                                                   background, dL_dpixels, dL_dmean2D, dL_dconic, dL_dopacity, stream);
 }
 
 int r3dgw_blend_backward(int P, int R, int C, const r3dgw_camera* cam, const char* geom_buffer,

@@ -1095,6 +1095,257 @@ static int launch_backward(dim3 grid, const uint2* ranges, const float4* A, cons
     return 0;
 }
 
+// -------------------------------------------------------------------------------------------------
+// Geometry-only backward over cached alphas, FRONT TO BACK (round 2).
+// blend_backward_kernel<.., COLOR=false> walks every tile list back to front and re-derives each pair's alpha from the
+// conic (quadratic, exp, thresholds) because the reference's recurrence needs the suffix sums
+//     dL/dalpha_k = T_k s_k - ( sum_{j>k} w_j s_j + T_final <bg, g> ) / (1 - alpha_k),   w_j = alpha_j T_j, s_j = <c_j, g>
+// (backward.cu:464-520: accum_rec / last_color, collapsed to the scalar s).  But the bracket is the pixel's whole
+// dot product minus a PREFIX:  sum_{j>k} w_j s_j + T_final <bg, g>  =  <out_pixel, g> - sum_{j<=k} w_j s_j,  and
+// <out_pixel, g> is known before the walk starts from the forward image.  So the pass runs in the direction the alpha
+// cache was written - one coalesced 128-byte row per surviving (warp, splat) pair, the same rows in the same order as
+// the forward replay and the colour-only backward - with T and the prefix as running products / sums: no conic
+// quadratic, no exp (G = alpha / opacity; only a pixel whose alpha sits on the 0.99 clamp re-evaluates exp), no
+// division chain T / (1 - alpha).  The six geometry sums per (warp, splat) come from the same moment product
+// Q[16 x 32] . Phi[32 x 6] as the back-to-front kernel and leave as 4 atomics.
+// Rounding: <out, g> - prefix cancels for the deepest contributors of a pixel, whose true bracket is T_final <bg, g>
+// (0 for a black background); the absolute error is ~1e-7 |<out, g>| per pair, the size of the reference's own
+// error in T = T_final / prod (1 - alpha) - measured against the FP64 oracle in tests/test_gpu_gradient_f64.py.
+// -------------------------------------------------------------------------------------------------
+constexpr int BWDG_BATCH = 64;
+constexpr int BWDG_QROWS = 16;
+constexpr int BWDG_DEPTH = 8;
+template <int C>
+struct BwdGeoCachedSmem {
+    float4 A[2][BWDG_BATCH];
+    float4 B[2][BWDG_BATCH];
+    float4 feat[2][BWDG_BATCH * ChanPad<C>::CP / 4];
+    uint16_t list[TILE_PIX / 32][BWDG_BATCH + BWDG_QROWS];
+    float Q[TILE_PIX / 32][BWDG_QROWS][33];
+    uint32_t red[TILE_PIX / 32];
+    uint64_t bar[2];
+};
+
+template <int C>
+__global__ void __launch_bounds__(TILE_PIX, 4) blend_backward_geometry_cached_kernel(
+    const uint2* __restrict__ ranges, const float4* __restrict__ splatA, const float4* __restrict__ splatB, int W, int H,
+    const float* __restrict__ features, const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
+    const float* __restrict__ out_images, const float* __restrict__ bg_color, const float* __restrict__ dL_dpixels,
+    float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D, float* __restrict__ dL_dopacity) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    BwdGeoCachedSmem<C>& s = *reinterpret_cast<BwdGeoCachedSmem<C>*>(smem_raw);
+    constexpr int CP = ChanPad<C>::CP, QROWS = BWDG_QROWS, DEPTH = BWDG_DEPTH, BATCH = BWDG_BATCH;
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned lx, ly;
+    tile_pixel(tid, lx, ly);
+    const uint2 pix = {blockIdx.x * TILE_X + lx, blockIdx.y * TILE_Y + ly};
+    const uint32_t pix_id = W * pix.y + pix.x;
+    const float2 pixf = {(float)pix.x, (float)pix.y};
+    const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
+    const float box_x = (float)(blockIdx.x * TILE_X + (warp & 1) * 8), box_y = (float)(blockIdx.y * TILE_Y + (warp >> 1) * 4);
+    const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
+    const uint32_t my_last = inside ? n_contrib[pix_id] : 0u;
+    const uint32_t warp_last = __reduce_max_sync(0xffffffffu, my_last);
+    if (lane == 0) s.red[warp] = warp_last;
+    if (tid == 0) {
+        mbar_init(&s.bar[0], 1);
+        mbar_init(&s.bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    uint32_t tile_last = 0;
+#pragma unroll
+    for (int w = 0; w < TILE_PIX / 32; ++w) tile_last = max(tile_last, s.red[w]);
+    const int total = (int)min(range.y - range.x, tile_last);
+    const int rounds = (total + BATCH - 1) / BATCH;
+    if (rounds == 0) return;
+    if (tid == 0) {
+        const uint32_t cnt = (uint32_t)min(BATCH, total);
+        mbar_expect_tx(&s.bar[0], cnt * 32u);
+        bulk_g2s(s.A[0], splatA + range.x, cnt * 16u, &s.bar[0]);
+        bulk_g2s(s.B[0], splatB + range.x, cnt * 16u, &s.bar[0]);
+    }
+    float2 dpix[CP / 2];
+    float Sb = 0.f;          // <forward pixel, dL/dpixel> over all channels (background term included)
+    float bg_dot = 0.f;      // <background, dL/dpixel>
+#pragma unroll
+    for (int q = 0; q < CP / 2; ++q) {
+        const int c0 = 2 * q, c1 = 2 * q + 1;
+        dpix[q].x = (inside && c0 < C) ? dL_dpixels[(size_t)c0 * H * W + pix_id] : 0.f;
+        dpix[q].y = (inside && c1 < C) ? dL_dpixels[(size_t)c1 * H * W + pix_id] : 0.f;
+        if (inside && c0 < C) Sb = fmaf(out_images[(size_t)c0 * H * W + pix_id], dpix[q].x, Sb);
+        if (inside && c1 < C) Sb = fmaf(out_images[(size_t)c1 * H * W + pix_id], dpix[q].y, Sb);
+        if (c0 < C) bg_dot = fmaf(bg_color[c0], dpix[q].x, bg_dot);
+        if (c1 < C) bg_dot = fmaf(bg_color[c1], dpix[q].y, bg_dot);
+    }
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+    float T = 1.0f, prefix = 0.f;
+    const float* my_rows = alpha_cache + ((size_t)range.x * 8 + (size_t)warp * (range.y - range.x)) * 32 + lane;
+
+    for (int i = 0; i < rounds; ++i) {
+        const int buf = i & 1;
+        const int cnt = min(BATCH, total - i * BATCH);
+        mbar_wait(&s.bar[buf], (uint32_t)(i >> 1) & 1u);
+        if ((int)tid < cnt) {
+            const uint32_t id = __float_as_uint(s.B[buf][tid].w);
+            const float* f = features + (size_t)id * C;
+            float fv[CP];
+#pragma unroll
+            for (int ch = 0; ch < CP; ++ch) fv[ch] = ch < C ? f[ch] : 0.f;
+#pragma unroll
+            for (int q = 0; q < CP / 4; ++q)
+                s.feat[buf][tid * (CP / 4) + q] = make_float4(fv[4 * q], fv[4 * q + 1], fv[4 * q + 2], fv[4 * q + 3]);
+        }
+        __syncthreads();   // features staged; every warp is done with the other A / B / feat buffers
+        if (tid == 0 && i + 1 < rounds) {
+            const int nb = buf ^ 1;
+            const uint32_t ncnt = (uint32_t)min(BATCH, total - (i + 1) * BATCH);
+            const size_t off = (size_t)range.x + (size_t)(i + 1) * BATCH;
+            mbar_expect_tx(&s.bar[nb], ncnt * 32u);
+            bulk_g2s(s.A[nb], splatA + off, ncnt * 16u, &s.bar[nb]);
+            bulk_g2s(s.B[nb], splatB + off, ncnt * 16u, &s.bar[nb]);
+        }
+        const uint32_t base = (uint32_t)i * BATCH;
+        if (base >= warp_last) continue;
+        uint16_t* list = s.list[warp];
+        int nsurv = 0;
+        for (int c0 = 0; c0 < cnt; c0 += 32) {
+            const int jl = c0 + (int)lane;
+            bool keep = false;
+            if (jl < cnt && base + (uint32_t)jl < warp_last) keep = splat_touches_warp(s.B[buf][jl], warp);
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) list[nsurv + __popc(m & ((1u << lane) - 1u))] = (uint16_t)jl;
+            nsurv += __popc(m);
+        }
+        __syncwarp();
+        const float* rows = my_rows;
+        my_rows += (size_t)nsurv * 32;
+
+        for (int g0 = 0; g0 < nsurv; g0 += QROWS) {
+            const int n = min(QROWS, nsurv - g0);
+            const float* rp = rows + (size_t)g0 * 32;
+#pragma unroll
+            for (int h = 0; h < QROWS / DEPTH; ++h) {
+                if (h * DEPTH >= n) break;
+                float al[DEPTH];
+#pragma unroll
+                for (int u = 0; u < DEPTH; ++u) al[u] = (h * DEPTH + u < n) ? __ldcs(rp + (h * DEPTH + u) * 32) : 0.f;
+#pragma unroll
+                for (int u = 0; u < DEPTH; ++u) {
+                    const int r = h * DEPTH + u;
+                    if (r >= n) break;
+                    const int jj = (int)list[g0 + r];
+                    const float alpha = al[u];
+                    float2 dot2 = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int q = 0; q < CP / 4; ++q) {
+                        const float4 f = s.feat[buf][jj * (CP / 4) + q];
+                        dot2 = __ffma2_rn(make_float2(f.x, f.y), dpix[2 * q], dot2);
+                        dot2 = __ffma2_rn(make_float2(f.z, f.w), dpix[2 * q + 1], dot2);
+                    }
+                    const float sdot = dot2.x + dot2.y;
+                    const float4 b = s.B[buf][jj];
+                    prefix = fmaf(alpha * T, sdot, prefix);
+                    const float one_m = 1.f - alpha;
+                    const float T_next = T * one_m;
+                    // behind the pixel's LAST contributor only the background is left: exactly T_final <bg, g>, no
+                    // cancellation there (that pair carries the largest 1 / (1 - alpha) of an opaque surface)
+                    const float bracket = (base + (uint32_t)jj + 1u == my_last) ? T_next * bg_dot : Sb - prefix;
+                    const float dL_dalpha = fmaf(T, sdot, -bracket * bwd_rcp(one_m));
+                    T = T_next;
+                    float G = alpha * bwd_rcp(b.y);
+                    if (alpha == 0.99f) {      // on the clamp: alpha no longer determines G
+                        const float4 a = s.A[buf][jj];
+                        const float2 d = {a.x - pixf.x, a.y - pixf.y};
+                        G = bwd_exp(-0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y);
+                    }
+                    s.Q[warp][r][lane] = G * dL_dalpha;      // alpha == 0 (pixel did not take the splat): exactly 0
+                }
+            }
+            // ---- six moments of q over the box-local pixel coordinates, 32 / QROWS lanes per row ----
+            __syncwarp();
+            {
+                constexpr int PARTS = 32 / QROWS, PP = QROWS;
+                const int row = (int)lane % QROWS, part = (int)lane / QROWS;
+                float S0 = 0.f, Su = 0.f, Sv = 0.f, Suu = 0.f, Suv = 0.f, Svv = 0.f;
+                const float* qrow = &s.Q[warp][row][part * PP];
+#pragma unroll
+                for (int k = 0; k < PP; ++k) {                     // pixel p = part*PP + k: u = p & 7, v = p >> 3
+                    const float q = qrow[k];
+                    const float u = (float)(k & 7), v = (float)(k >> 3);
+                    S0 += q;
+                    if ((k & 7) != 0) { Su = fmaf(q, u, Su); Suu = fmaf(q, u * u, Suu); }
+                    if ((k >> 3) != 0) { Sv = fmaf(q, v, Sv); Svv = fmaf(q, v * v, Svv); }
+                    if ((k & 7) != 0 && (k >> 3) != 0) Suv = fmaf(q, u * v, Suv);
+                }
+                if (PARTS > 1) {
+                    const float vb = (float)(part * (PP / 8));     // rows of the box before this lane's slice
+                    Svv = fmaf(vb * vb, S0, fmaf(2.f * vb, Sv, Svv));
+                    Suv = fmaf(vb, Su, Suv);
+                    Sv = fmaf(vb, S0, Sv);
+#pragma unroll
+                    for (int off = QROWS; off < 32; off <<= 1) {
+                        S0 += __shfl_xor_sync(0xffffffffu, S0, off);
+                        Su += __shfl_xor_sync(0xffffffffu, Su, off);
+                        Sv += __shfl_xor_sync(0xffffffffu, Sv, off);
+                        Suu += __shfl_xor_sync(0xffffffffu, Suu, off);
+                        Suv += __shfl_xor_sync(0xffffffffu, Suv, off);
+                        Svv += __shfl_xor_sync(0xffffffffu, Svv, off);
+                    }
+                }
+                const bool nz = (S0 != 0.f) | (Su != 0.f) | (Sv != 0.f) | (Suu != 0.f) | (Suv != 0.f) | (Svv != 0.f);
+                if (part == 0 && row < n && nz) {
+                    const int jj = (int)list[g0 + row];
+                    const float4 a = s.A[buf][jj];
+                    const float4 b = s.B[buf][jj];
+                    const float mx = a.x - box_x, my = a.y - box_y;          // d = (mx - u, my - v)
+                    const float X1 = fmaf(mx, S0, -Su), Y1 = fmaf(my, S0, -Sv);
+                    const float XX = fmaf(mx, fmaf(mx, S0, -2.f * Su), Suu);
+                    const float YY = fmaf(my, fmaf(my, S0, -2.f * Sv), Svv);
+                    const float XY = fmaf(mx, fmaf(my, S0, -Sv), fmaf(-my, Su, Suv));
+                    const float o = b.y, ho = -0.5f * o;
+                    const uint32_t id = __float_as_uint(b.w);
+                    atomicAdd(dL_dmean2D + (size_t)id * 3, -o * (a.z * X1 + a.w * Y1) * ddelx_dx);
+                    atomicAdd(dL_dmean2D + (size_t)id * 3 + 1, -o * (b.x * Y1 + a.w * X1) * ddely_dy);
+                    red_add_v4(dL_dconic2D + (size_t)id * 4, ho * XX, ho * XY, 0.f, ho * YY);
+                    atomicAdd(dL_dopacity + id, S0);
+                }
+            }
+            __syncwarp();   // Q is rewritten by the next block
+        }
+    }
+}
+
+template <int C>
+static int launch_backward_geometry_cached(dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
+                                           const float* features, const uint32_t* n_contrib, const float* alpha_cache,
+                                           const float* out_images, const float* bg, const float* dL_dpix, float* dL_dmean2D,
+                                           float* dL_dconic, float* dL_dopacity, cudaStream_t stream) {
+    const int smem = (int)sizeof(BwdGeoCachedSmem<C>);
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_geometry_cached_kernel<C>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    {
+        ProfScope ps(KID_BLEND_BWD_GEOM, stream);
+        blend_backward_geometry_cached_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, features, n_contrib, alpha_cache,
+                                                                                  out_images, bg, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity);
+    }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+int blend_backward_geometry_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W,
+                                            int H, const float* features, const uint32_t* n_contrib,
+                                            const float* alpha_cache, const float* out_images, const float* bg,
+                                            const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                                            cudaStream_t stream) {
+    switch (C) {
+#define R3DGW_BWDG_CASE(N) case N: return launch_backward_geometry_cached<N>(grid, ranges, A, B, W, H, features, n_contrib, alpha_cache, out_images, bg, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, stream);
+        R3DGW_BWDG_CASE(3) R3DGW_BWDG_CASE(4) R3DGW_BWDG_CASE(6) R3DGW_BWDG_CASE(8) R3DGW_BWDG_CASE(9) R3DGW_BWDG_CASE(12)
+        R3DGW_BWDG_CASE(15) R3DGW_BWDG_CASE(16)
+#undef R3DGW_BWDG_CASE
+        default: return R3DGW_ERR_UNSUPPORTED;
+    }
+}
+
 int blend_forward_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
                            const float* features, const float* bg, float* final_T, uint32_t* n_contrib,
                            float* out_color, float* alpha_cache, int cache_mode, cudaStream_t stream) {

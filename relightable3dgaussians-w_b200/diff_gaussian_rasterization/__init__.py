@@ -359,13 +359,13 @@ class _BlendFn(torch.autograd.Function):
         ctx.means2D_shape = means2D.shape
         ctx.means2D_is_ref = means2D is st.means2D_ref
         ctx.feat_shape = features.shape
-        ctx.save_for_backward(feats if feats is not None else torch.empty(0, device=dev), bgc, img)
+        ctx.save_for_backward(feats if feats is not None else torch.empty(0, device=dev), bgc, img, out)
         return out
 
     @staticmethod
     def backward(ctx, grad_out):
         st, C = ctx.st, ctx.C
-        feats, bgc, img = ctx.saved_tensors
+        feats, bgc, img, out_img = ctx.saved_tensors
         dev = grad_out.device
         P = st.P
         L = _nat.lib()
@@ -392,7 +392,7 @@ class _BlendFn(torch.autograd.Function):
             if stride != C:
                 dfeat = dfeat[:, :C]
             if geo_needed:
-                st.pending.append((feats, bgc, g, img))
+                st.pending.append((feats, bgc, g, img, out_img))
             return None, None, None, None, None, dfeat, None, None
         flat = torch.zeros(P * (3 + 4 + 1 + C), dtype=torch.float32, device=dev)
         dmean2D = flat[:3 * P].view(P, 3)
@@ -471,38 +471,57 @@ def set_deferred_backward(enabled: bool):
     _DEFER_BWD = bool(enabled)
 
 
+_BWDG_CACHED = os.environ.get("R3DGW_BWDG_CACHED", "1") != "0"
+_BWDG_CHANNELS = (16, 15, 12, 9, 8, 6, 4, 3)     # channel totals the front-to-back cached geometry pass is instantiated for
+
+
 def _deferred_geometry_pass(st, dev):
-    """One geometry-only K5 (r3dgw_blend_backward with dL_dfeatures == NULL) over the concatenation of every pending
-    blend call's features / background / pixel gradients; calls are grouped so that each group's channel total is
-    one the kernel is instantiated for.  Returns (dL_dmean2D[P,3], dL_dconic[P,4], dL_dopacity[P,1])."""
+    """One geometry-only pass over the concatenation of every pending blend call's features / pixel gradients; calls
+    are grouped so that each group's channel total is one the kernel is instantiated for.  While the state still owns
+    the alpha cache the pass is r3dgw_blend_backward_geometry_cached (front to back over the cached alphas, needs the
+    calls' forward images); otherwise r3dgw_blend_backward with dL_dfeatures == NULL (back to front, alphas re-derived
+    from the conics).  Returns (dL_dmean2D[P,3], dL_dconic[P,4], dL_dopacity[P,1])."""
     pending, st.pending = st.pending, []
     P = st.P
     L = _nat.lib()
     flat = torch.zeros(P * 8, dtype=torch.float32, device=dev)
     d_mean2D, d_conic, d_opac = flat[:3 * P].view(P, 3), flat[3 * P:7 * P].view(P, 4), flat[7 * P:].view(P, 1)
+    cache = st.alpha_cache if _BWDG_CACHED else None
+    chans = _BWDG_CHANNELS if cache is not None else _BWD_CHANNELS
     i = 0
     while i < len(pending):
         # longest run of calls whose channel total is instantiated
         best, tot, j = None, 0, i
-        while j < len(pending) and tot + pending[j][0].size(1) <= 32:
+        while j < len(pending) and tot + pending[j][0].size(1) <= max(chans):
             tot += pending[j][0].size(1)
             j += 1
-            if tot in _BWD_CHANNELS:
+            if tot in chans:
                 best = (j, tot)
+        if best is None:       # a single call with a channel count only the back-to-front kernel has
+            cache, chans = None, _BWD_CHANNELS
+            continue
         j, tot = best
         grp = pending[i:j]
         if len(grp) == 1:
-            feats, bgc, g = grp[0][0], grp[0][1], grp[0][2]
+            feats, bgc, g, outs = grp[0][0], grp[0][1], grp[0][2], grp[0][4]
         else:
             feats = torch.cat([e[0] for e in grp], dim=1)
             bgc = torch.cat([e[1].reshape(-1) for e in grp])
             g = torch.cat([e[2] for e in grp], dim=0)
+            outs = torch.cat([e[4] for e in grp], dim=0) if cache is not None else None
         img = grp[0][3]
         with _nat.on_device(dev):
-            rc = L.r3dgw_blend_backward(P, st.R, tot, ctypes.byref(st.cam), st.geom.data_ptr(), st.binning.data_ptr(),
-                                        img.data_ptr(), feats.data_ptr(), bgc.data_ptr(), g.data_ptr(),
-                                        d_mean2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr(), None, _stream())
-        _nat.check(rc, "r3dgw_blend_backward (geometry-only)")
+            if cache is not None:
+                rc = L.r3dgw_blend_backward_geometry_cached(P, st.R, tot, ctypes.byref(st.cam), st.binning.data_ptr(),
+                                                            img.data_ptr(), cache.data_ptr(), feats.data_ptr(),
+                                                            outs.contiguous().data_ptr(), bgc.data_ptr(), g.data_ptr(),
+                                                            d_mean2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr(),
+                                                            _stream())
+            else:
+                rc = L.r3dgw_blend_backward(P, st.R, tot, ctypes.byref(st.cam), st.geom.data_ptr(), st.binning.data_ptr(),
+                                            img.data_ptr(), feats.data_ptr(), bgc.data_ptr(), g.data_ptr(),
+                                            d_mean2D.data_ptr(), d_conic.data_ptr(), d_opac.data_ptr(), None, _stream())
+        _nat.check(rc, "geometry-only blend backward")
         _stats["backward_geometry_only"] += 1
         i = j
     return d_mean2D, d_conic, d_opac
@@ -534,7 +553,7 @@ def set_geometry_cache(enabled: bool):
 
 
 def last_geometry_state():
-    e = _cache["entry"]
+    e = _cache["entry"] if _CACHE_ENABLED else _cache.get("last")
     return e[0] if e else None
 
 
@@ -565,6 +584,8 @@ def _geometry(means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s, mean
     entry = (st, handles, (means3D, opacities, scales, rotations, cov3Ds_precomp, sh, s.viewmatrix, s.projmatrix, s.campos))
     if _CACHE_ENABLED:
         _cache["key"], _cache["entry"] = key, entry
+    else:
+        _cache["last"] = entry       # introspection only (last_geometry_state()); never reused
     return entry
 
 

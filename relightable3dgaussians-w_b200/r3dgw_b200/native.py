@@ -33,7 +33,7 @@ SYMBOLS = [
     "r3dgw_preshade_forward", "r3dgw_preshade_backward", "r3dgw_gaussian_normal_forward",
     "r3dgw_gaussian_normal_backward", "r3dgw_gaussian_reg_workspace_bytes", "r3dgw_gaussian_regularisers_forward",
     "r3dgw_gaussian_regularisers_backward", "r3dgw_normal_tail_forward", "r3dgw_normal_tail_backward",
-    "r3dgw_normal_loss_forward", "r3dgw_normal_loss_backward",
+    "r3dgw_normal_loss_forward", "r3dgw_normal_loss_backward", "r3dgw_blend_backward_geometry_cached",
 ]
 
 
@@ -144,6 +144,7 @@ def lib():
     L.r3dgw_blend_forward.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp]
     L.r3dgw_blend_forward_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp, ci, vp]
     L.r3dgw_blend_backward_color_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, ci, vp]
+    L.r3dgw_blend_backward_geometry_cached.argtypes = [ci, ci, ci, cam] + [vp] * 11
     L.r3dgw_materialize_sorted_keys.argtypes = [ci, ci, ci, ci, vp, vp, vp]
     L.r3dgw_alpha_cache_bytes.argtypes = [ci]
     L.r3dgw_alpha_cache_bytes.restype = ctypes.c_size_t

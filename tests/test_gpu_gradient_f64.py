@@ -7,7 +7,8 @@ double, evaluated over the reference's OWN forward buffers.  Enforced per gradie
 B (the config every bench number is quoted on), for the single U1 call and for render()'s six-call pattern:
 
     ||new - f64||_2 <= 1e-4 ||f64||_2                  (north_star asks <= 1e-3 relative; measured: <= 2.2e-5)
-    ||new - f64||_2 <= 1.5 ||ref - f64||_2 + 1e-6 ||f64||_2   (never less accurate than the reference's own kernels)
+    ||new - f64||_2 <= k ||ref - f64||_2 + 1e-6 ||f64||_2    (k = 1.5 for the back-to-front geometry pass; k = 4 with the
+                                                               default front-to-back cached pass, see REF_FACTOR below)
     99.99 % of entries: |new - f64| <= 1e-3 |f64| + 1e-5 max|f64|
 (The reference itself sits at 6e-4 .. 1e-3 on rotations and 1e-4 .. 2e-4 on scales at A / B: its float evaluation of
 the cov2D -> cov3D -> quaternion chain cancels heavily.  The new fused geometry backward evaluates that chain in FP64
@@ -61,7 +62,13 @@ def _run(mod, sc, feats, bgs, dLs):
 import os
 F32_CHAIN = os.environ.get("R3DGW_GEOM_BWD_F32", "0") == "1"
 L2_BAR = 1.5e-3 if F32_CHAIN else 1e-4
-REF_FACTOR = 2.5 if F32_CHAIN else 1.5
+# The default geometry pass of a multi-blend frame walks the alpha cache front to back and forms the reference's suffix
+# sums as <forward pixel, dL/dpixel> minus a running prefix (csrc/blend.cu, blend_backward_geometry_cached_kernel): that
+# subtraction costs a factor 2-3 on the SCREEN-SPACE gradients' error (3e-6 instead of 1.2e-6 relative L2 at config B -
+# both 30x inside the 1e-4 bar) for a pass that is 26 % faster.  R3DGW_BWDG_CACHED=0 selects the back-to-front pass,
+# which is held to 1.5x the reference's own error.
+BWDG_CACHED = os.environ.get("R3DGW_BWDG_CACHED", "1") != "0"
+REF_FACTOR = 2.5 if F32_CHAIN else (4.0 if BWDG_CACHED else 1.5)
 STRICT_FRAC = 0.999 if F32_CHAIN else 0.9999
 
 
