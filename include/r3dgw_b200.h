@@ -32,6 +32,7 @@ extern "C" {
 #define R3DGW_ERR_UNSUPPORTED  (-2)  /* channel count not instantiated, SH degree > 3, ...        */
 #define R3DGW_ERR_ALLOC        (-3)  /* an allocation callback returned NULL                      */
 #define R3DGW_ERR_OVERFLOW     (-4)  /* num_rendered would exceed 2^31-1 (reference cap, 32-bit)  */
+#define R3DGW_ERR_TOO_LARGE    (-5)  /* size beyond the static scratch of an allocation-free entry point */
 
 #define R3DGW_MAX_CHANNELS 32
 
@@ -330,6 +331,22 @@ int r3dgw_gaussian_regularisers_forward(int P, const int* radii, const uint8_t* 
 int r3dgw_gaussian_regularisers_backward(int P, const int* radii, const uint8_t* is_sky, const float* scales,
                                          const float* viewmatrix, float gamma, const float* out,
                                          const float* grads, float* dL_dscales, float* dL_dmeans3D, void* stream);
+/* Allocation-free variant of r3dgw_gaussian_regularisers_forward.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same inputs, same `out`, same kernels and reduction order (results are
+ * bit-identical to the workspace entry point); the per-CTA partial sums live in a file-scope
+ * `static __device__ __align__(256)` array of 28 416 bytes that every GPU loading the library holds until exit,
+ * resolved once per device with cudaGetSymbolAddress (that device must be current at the call, as for every entry
+ * point here).  Calls no cudaMalloc / cudaFree / allocating library routine and ignores r3dgw_profile_enable.
+ * Limit: P <= r3dgw_gaussian_regularisers_noalloc_max_gaussians() = 16 777 216 Gaussians (2^24, up to which the f32 counts
+ * in out[2], out[3], out[6] are exact); a larger P returns R3DGW_ERR_TOO_LARGE (and says so on stderr) without
+ * launching anything.  Every call on a device shares the one array, which keeps the last call's contents (nothing
+ * in it has to start at zero: each call overwrites every slot it later reads): calls that OVERLAP on the GPU
+ * (different streams without an ordering between them) RACE - serialise them. */
+int r3dgw_gaussian_regularisers_noalloc_max_gaussians(void);
+int r3dgw_gaussian_regularisers_forward_noalloc(int P, const int* radii, const uint8_t* is_sky, const float* scales,
+                                                const float* means3D, const float* viewmatrix, float gamma,
+                                                float* out, void* stream);
 
 /* ---- image-space post-ops of the training step ---------------------------------
  * Replace torch graphs in the reference (paths relative to /root/reference):

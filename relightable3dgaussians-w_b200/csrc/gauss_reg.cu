@@ -9,6 +9,8 @@
 // (29 B per Gaussian); per-CTA partial sums are reduced in a fixed order by a one-block finalize kernel, so the two
 // losses are bit-reproducible and nothing returns to the host.
 #include "common.cuh"
+#include <algorithm>
+#include <cstdio>
 
 namespace r3dgw {
 
@@ -141,6 +143,69 @@ extern "C" int r3dgw_gaussian_regularisers_backward(int P, const int* radii, con
         gaussian_reg_backward_kernel<<<(P + REG_THREADS - 1) / REG_THREADS, REG_THREADS, 0, stream>>>(
             P, radii, is_sky, scales, viewmatrix, gamma, out, grads, dL_dscales, dL_dmeans3D);
     }
+    R3DGW_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---- allocation-free variant (no counterpart in the reference) -----
+// Callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it)
+// get the forward pass with its per-CTA partial sums in a file-scope device array instead of a caller workspace.
+// Every GPU that loads the library holds the array (REG_MAX_BLOCKS * REG_VALS doubles = 28 416 B) until exit.
+// g_reg_scratch is a HOST-SIDE STAND-IN in host code, not a device address: the address the kernels get comes from
+// cudaGetSymbolAddress, resolved once per device with that device current.
+namespace r3dgw {
+
+constexpr int REG_NOALLOC_MAX_P = 1 << 24;   // the f32 counts in out[2], out[3], out[6] are exact up to 2^24
+constexpr int REG_NOALLOC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) double g_reg_scratch[REG_MAX_BLOCKS * REG_VALS];
+static std::atomic<double*> g_reg_scratch_addr[REG_NOALLOC_MAX_DEVICES];   // zero-initialised: not resolved yet
+
+// -> 0 and *ptr = device address of g_reg_scratch on the CURRENT device, or a cudaError_t value
+static int reg_scratch_for_current_device(double** ptr) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= REG_NOALLOC_MAX_DEVICES) return R3DGW_ERR_UNSUPPORTED;
+    double* p = g_reg_scratch_addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        // set-up, once per device (a concurrent first call resolves the same address twice: harmless)
+        e = cudaGetSymbolAddress((void**)&p, g_reg_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return (int)cudaErrorInvalidSymbol;
+        g_reg_scratch_addr[dev].store(p, std::memory_order_release);
+    }
+    *ptr = p;
+    return 0;
+}
+
+}  // namespace r3dgw
+
+extern "C" int r3dgw_gaussian_regularisers_noalloc_max_gaussians(void) { return REG_NOALLOC_MAX_P; }
+
+extern "C" int r3dgw_gaussian_regularisers_forward_noalloc(int P, const int* radii, const uint8_t* is_sky,
+                                                           const float* scales, const float* means3D,
+                                                           const float* viewmatrix, float gamma, float* out,
+                                                           void* stream_) {
+    if (P < 0 || !out || !viewmatrix) return R3DGW_ERR_BAD_ARG;
+    if (P > 0 && (!radii || !scales || !means3D)) return R3DGW_ERR_BAD_ARG;
+    if (P > REG_NOALLOC_MAX_P) {
+        fprintf(stderr, "r3dgw_gaussian_regularisers_forward_noalloc: P = %d exceeds the maximum of %d Gaussians of the "
+                        "allocation-free entry point; use r3dgw_gaussian_regularisers_forward with a caller workspace\n",
+                P, REG_NOALLOC_MAX_P);
+        return R3DGW_ERR_TOO_LARGE;
+    }
+    double* scratch = nullptr;
+    const int rc = reg_scratch_for_current_device(&scratch);
+    if (rc != 0) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int blocks = reg_blocks(P);   // <= REG_MAX_BLOCKS for every P: the array always holds the partial sums
+    // nothing in the scratch has to start at zero: every CTA overwrites its REG_VALS slots unconditionally and the
+    // finalize kernel reads exactly the `blocks` rows this call wrote (whatever the last call left behind the row
+    // `blocks` is never read).  No ProfScope here: the profiler creates events.
+    gaussian_reg_partial_kernel<<<blocks, REG_THREADS, 0, stream>>>(P, radii, is_sky, scales, means3D, viewmatrix, scratch);
+    R3DGW_LAUNCH_CHECK();
+    gaussian_reg_finalize_kernel<<<1, 32, 0, stream>>>(blocks, scratch, gamma, out);
     R3DGW_LAUNCH_CHECK();
     return 0;
 }

@@ -34,6 +34,7 @@ SYMBOLS = [
     "r3dgw_gaussian_normal_backward", "r3dgw_gaussian_reg_workspace_bytes", "r3dgw_gaussian_regularisers_forward",
     "r3dgw_gaussian_regularisers_backward", "r3dgw_normal_tail_forward", "r3dgw_normal_tail_backward",
     "r3dgw_normal_loss_forward", "r3dgw_normal_loss_backward", "r3dgw_blend_backward_geometry_cached",
+    "r3dgw_gaussian_regularisers_noalloc_max_gaussians", "r3dgw_gaussian_regularisers_forward_noalloc",
 ]
 
 
@@ -170,6 +171,8 @@ def lib():
     L.r3dgw_gaussian_reg_workspace_bytes.restype = sz
     L.r3dgw_gaussian_regularisers_forward.argtypes = [ci, vp, vp, vp, vp, vp, ctypes.c_float, vp, vp, vp]
     L.r3dgw_gaussian_regularisers_backward.argtypes = [ci, vp, vp, vp, vp, ctypes.c_float, vp, vp, vp, vp, vp]
+    L.r3dgw_gaussian_regularisers_noalloc_max_gaussians.argtypes = []
+    L.r3dgw_gaussian_regularisers_forward_noalloc.argtypes = [ci, vp, vp, vp, vp, vp, ctypes.c_float, vp, vp]
     L.r3dgw_envmap_sh_render.argtypes = [ci, vp, ci, vp, vp]
     L.r3dgw_image_loss_workspace_bytes.argtypes = [ci, ci, ci]
     L.r3dgw_image_loss_workspace_bytes.restype = sz
@@ -223,7 +226,8 @@ class R3dgwError(RuntimeError):
 
 
 _ERR = {-1: "bad argument", -2: "unsupported configuration", -3: "allocation callback failed",
-        -4: "num_rendered overflows 32-bit int"}
+        -4: "num_rendered overflows 32-bit int",
+        -5: "size exceeds the static scratch of the allocation-free entry point"}
 
 
 def check(rc, what):

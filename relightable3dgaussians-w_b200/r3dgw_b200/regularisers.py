@@ -83,3 +83,27 @@ def depth_loss_gaussians(gaussians, camera, visibility_filter, gamma=0.02):
     xyz = gaussians.get_xyz
     return gaussian_regularisers(torch.ones_like(xyz), xyz, visibility_filter.to(torch.int32), gaussians.get_is_sky,
                                  camera.world_view_transform, gamma)[1]
+
+
+def gaussian_regularisers_forward_noalloc(scales, means3D, radii, is_sky_u8, viewmatrix, gamma, out):
+    """Allocation-free forward (no counterpart in the reference; for callers that cannot call cudaMalloc, e.g. under
+    CUDA graph capture): fills the caller's f32[8] `out` with the statistics of `gaussian_regularisers` and returns it.
+    Nothing is converted or copied here (that would allocate): every tensor must already be a contiguous CUDA tensor
+    of the dtype the C-ABI takes (f32 scales / means3D / viewmatrix / out, int32 radii, uint8 is_sky or None).  The
+    partial sums live in a static device array shared by all calls on a GPU: calls that overlap on the GPU race.
+    P above `r3dgw_gaussian_regularisers_noalloc_max_gaussians()` (2^24) raises."""
+    f32 = torch.float32
+    for name, t, dt in (("scales", scales, f32), ("means3D", means3D, f32), ("radii", radii, torch.int32),
+                        ("viewmatrix", viewmatrix, f32), ("out", out, f32)) + \
+            ((("is_sky_u8", is_sky_u8, torch.uint8),) if is_sky_u8 is not None else ()):
+        if t.device.type != "cuda" or t.dtype != dt or not t.is_contiguous():
+            raise RuntimeError(f"gaussian_regularisers_forward_noalloc: `{name}` must be a contiguous {dt} CUDA tensor")
+    if out.numel() < 8:
+        raise RuntimeError("gaussian_regularisers_forward_noalloc: `out` needs 8 floats")
+    P = int(scales.shape[0])
+    with _nat.on_device(scales.device):
+        rc = _nat.lib().r3dgw_gaussian_regularisers_forward_noalloc(
+            P, radii.data_ptr(), None if is_sky_u8 is None else is_sky_u8.data_ptr(), scales.data_ptr(),
+            means3D.data_ptr(), viewmatrix.data_ptr(), float(gamma), out.data_ptr(), _nat.raw_stream())
+    _nat.check(rc, "r3dgw_gaussian_regularisers_forward_noalloc")
+    return out
