@@ -197,6 +197,17 @@ int r3dgw_blend_backward_geometry_cached(int P, int R, int C, const r3dgw_camera
                                          const char* image_buffer, const float* alpha_cache, const float* features,
                                          const float* out_images, const float* background, const float* dL_dpixels,
                                          float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, void* stream);
+/* The same pass over n_calls blend calls whose tensors stay where they are (no concatenation copies): channels[i]
+ * (host array; their sum must be one of the totals above, <= 16), and HOST arrays of n_calls DEVICE pointers:
+ * features[i] f32[P, channels[i]], out_images[i] / dL_dpixels[i] f32[channels[i], H, W], backgrounds[i]
+ * f32[channels[i]].  This is how the six-call pattern of render() (gaussian_renderer/__init__.py:160-264) reaches
+ * the pass: one geometry-gradient walk for the five differentiated calls. */
+int r3dgw_blend_backward_geometry_cached_calls(int P, int R, int n_calls, const int* channels, const r3dgw_camera* cam,
+                                               const char* binning_buffer, const char* image_buffer,
+                                               const float* alpha_cache, const float* const* features,
+                                               const float* const* out_images, const float* const* backgrounds,
+                                               const float* const* dL_dpixels, float* dL_dmean2D, float* dL_dconic,
+                                               float* dL_dopacity, void* stream);
 
 /* K6+K7 fused: conic/mean2D gradients -> means3D, cov3D, scales, rotations (and SH).
  * Overwrites dL_dmean3D/dL_dcov3D/dL_dscale/dL_drot rows of visible Gaussians (caller zeroes).

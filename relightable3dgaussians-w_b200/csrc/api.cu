@@ -57,11 +57,12 @@ int blend_backward_dispatch(int C, dim3 grid, const uint2* ranges, const float4*
 int blend_backward_color_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* B, int W, int H,
                                          const uint32_t* n_contrib, const float* alpha_cache, const float* dL_dpix,
                                          float* dL_dfeatures, int grad_stride, cudaStream_t stream);
-int blend_backward_geometry_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W,
-                                            int H, const float* features, const uint32_t* n_contrib,
-                                            const float* alpha_cache, const float* out_images, const float* bg,
-                                            const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
-                                            cudaStream_t stream);
+int blend_backward_geometry_cached_dispatch(int n_calls, const int* channels, dim3 grid, const uint2* ranges, const float4* A,
+                                            const float4* B, int W, int H, const float* const* features,
+                                            const uint32_t* n_contrib, const float* alpha_cache,
+                                            const float* const* out_images, const float* const* bg,
+                                            const float* const* dL_dpix, float* dL_dmean2D, float* dL_dconic,
+                                            float* dL_dopacity, cudaStream_t stream);
 int sort_num_passes(int end_bit);
 
 static inline int pre_blocks(int P) { return (P + PRE_THREADS - 1) / PRE_THREADS; }
@@ -299,9 +300,16 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
 
     {
         ProfScope ps(KID_RANGES, stream);
-        ranges_gather_kernel<<<(R + 255) / 256, 256, 0, stream>>>(
-            (int)R, tk_main, vals_main, (const float2*)(g + GL.means2D), (const float4*)(g + GL.conic_opacity),
-            (uint2*)(b + BL.ranges), (float4*)(b + BL.splats), (float4*)(b + BL.splats) + R, gx);
+        // R3DGW_CULL_V2=0: the per-footprint edge minimisation (splat_may_touch) instead of the shared-line form
+        static const bool cull_v2 = [] { const char* e = getenv("R3DGW_CULL_V2"); return !(e && e[0] == '0'); }();
+        if (cull_v2)
+            ranges_gather_kernel<true><<<(R + 255) / 256, 256, 0, stream>>>(
+                (int)R, tk_main, vals_main, (const float2*)(g + GL.means2D), (const float4*)(g + GL.conic_opacity),
+                (uint2*)(b + BL.ranges), (float4*)(b + BL.splats), (float4*)(b + BL.splats) + R, gx);
+        else
+            ranges_gather_kernel<false><<<(R + 255) / 256, 256, 0, stream>>>(
+                (int)R, tk_main, vals_main, (const float2*)(g + GL.means2D), (const float4*)(g + GL.conic_opacity),
+                (uint2*)(b + BL.ranges), (float4*)(b + BL.splats), (float4*)(b + BL.splats) + R, gx);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;
@@ -369,12 +377,14 @@ int r3dgw_blend_backward_color_cached(int P, int R, int C, const r3dgw_camera* c
                                                 dL_dpixels, dL_dfeatures, grad_stride, stream);
 }
 
-int r3dgw_blend_backward_geometry_cached(int P, int R, int C, const r3dgw_camera* cam, const char* binning_buffer,
-                                         const char* image_buffer, const float* alpha_cache, const float* features,
-                                         const float* out_images, const float* background, const float* dL_dpixels,
-                                         float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, void* stream_) {
-    if (!cam || !binning_buffer || !image_buffer || !features || !out_images || !background || !dL_dpixels || !dL_dmean2D || !dL_dconic ||
-        !dL_dopacity || R < 0 || P < 0)
+int r3dgw_blend_backward_geometry_cached_calls(int P, int R, int n_calls, const int* channels, const r3dgw_camera* cam,
+                                               const char* binning_buffer, const char* image_buffer,
+                                               const float* alpha_cache, const float* const* features,
+                                               const float* const* out_images, const float* const* backgrounds,
+                                               const float* const* dL_dpixels, float* dL_dmean2D, float* dL_dconic,
+                                               float* dL_dopacity, void* stream_) {
+    if (!cam || !binning_buffer || !image_buffer || n_calls <= 0 || !channels || !features || !out_images || !backgrounds ||
+        !dL_dpixels || !dL_dmean2D || !dL_dconic || !dL_dopacity || R < 0 || P < 0)
         return R3DGW_ERR_BAD_ARG;
     if (R == 0) return 0;
     if (!alpha_cache) return R3DGW_ERR_BAD_ARG;
@@ -384,9 +394,19 @@ int r3dgw_blend_backward_geometry_cached(int P, int R, int C, const r3dgw_camera
     r3dgw_image_layout IL; image_layout(W, H, &IL);
     dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
     const float4* A = (const float4*)(binning_buffer + BL.splats);
-    return blend_backward_geometry_cached_dispatch(C, grid, (const uint2*)(binning_buffer + BL.ranges), A, A + R, W, H, features,
-                                                   (const uint32_t*)(image_buffer + IL.n_contrib), alpha_cache, out_images,
-                                                   background, dL_dpixels, dL_dmean2D, dL_dconic, dL_dopacity, stream);
+    return blend_backward_geometry_cached_dispatch(n_calls, channels, grid, (const uint2*)(binning_buffer + BL.ranges), A, A + R,
+                                                   W, H, features, (const uint32_t*)(image_buffer + IL.n_contrib), alpha_cache,
+                                                   out_images, backgrounds, dL_dpixels, dL_dmean2D, dL_dconic, dL_dopacity,
+                                                   stream);
+}
+
+int r3dgw_blend_backward_geometry_cached(int P, int R, int C, const r3dgw_camera* cam, const char* binning_buffer,
+                                         const char* image_buffer, const float* alpha_cache, const float* features,
+                                         const float* out_images, const float* background, const float* dL_dpixels,
+                                         float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, void* stream_) {
+    return r3dgw_blend_backward_geometry_cached_calls(P, R, 1, &C, cam, binning_buffer, image_buffer, alpha_cache, &features,
+                                                      &out_images, &background, &dL_dpixels, dL_dmean2D, dL_dconic,
+                                                      dL_dopacity, stream_);
 }
 
 int r3dgw_blend_backward(int P, int R, int C, const r3dgw_camera* cam, const char* geom_buffer,

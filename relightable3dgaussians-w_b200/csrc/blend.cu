@@ -95,7 +95,7 @@ struct FwdSmem {
 // effective alphas (0 where the pixel did not take the splat) as one 128-byte row of `alpha_cache`
 // (row = list position, 256 floats per entry indexed by thread id).  Later blends over the same geometry
 // (blend_forward_cached_kernel) replay those rows instead of re-evaluating the conic / exp / threshold chain.
-template <int C, bool WRITE_CACHE>
+template <int C, bool WRITE_CACHE, bool FLAT = false>
 __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatA, const float4* __restrict__ splatB,
     int W, int H, const float* __restrict__ features, const float* __restrict__ bg_color,
@@ -179,7 +179,36 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                 const int j = c0 + __ffs(m) - 1;
                 m &= m - 1;
                 float a_eff = 0.f;   // alpha this pixel actually blended with (0: skipped / done)
-                if (!done) {
+                if constexpr (FLAT) {
+                    // branch-free walk: same expressions and decisions, evaluated by every lane and applied under
+                    // one predicate (the breaks of the branchy form cost a reconvergence scope, three branches and
+                    // byte-packed flags per row; a lane that would have left early only skips work when the whole
+                    // warp does, which the footprint cull has already made rare)
+                    const float4 a = s.A[buf][j];
+                    const float4 b = s.B[buf][j];
+                    const float2 d = {a.x - pixf.x, a.y - pixf.y};
+                    const float power = -0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y;
+                    const float alpha = min(0.99f, b.y * exp(power));
+                    const float test_T = T * (1 - alpha);
+                    // !(x > 0) && !(x < thr) keeps the branchy form's NaN behaviour (a NaN power goes on to alpha)
+                    const bool cand = !done & !(power > 0.0f) & !(power < b.z) & !(alpha < 1.0f / 255.0f);
+                    const bool stop = cand & (test_T < 0.0001f);
+                    const bool take = cand & !stop;
+                    done |= stop;
+                    const float w = take ? alpha * T : 0.f;
+                    const float2 w2 = make_float2(w, w);
+                    if (take) {
+#pragma unroll
+                        for (int q = 0; q < CP / 4; ++q) {
+                            const float4 f = s.feat[buf][j * (CP / 4) + q];
+                            Cacc[2 * q] = __ffma2_rn(make_float2(f.x, f.y), w2, Cacc[2 * q]);
+                            Cacc[2 * q + 1] = __ffma2_rn(make_float2(f.z, f.w), w2, Cacc[2 * q + 1]);
+                        }
+                        T = test_T;
+                        last_contributor = base + (uint32_t)j + 1u;
+                        a_eff = alpha;
+                    }
+                } else if (!done) {
                     do {
                         const float4 a = s.A[buf][j];
                         const float4 b = s.B[buf][j];
@@ -1064,17 +1093,21 @@ static int launch_forward(dim3 grid, const uint2* ranges, const float4* A, const
         return 0;
     }
     const int smem = (int)sizeof(FwdSmem<C>);
+    // R3DGW_FWD_FLAT=0: the branchy per-row walk (A/B)
+    static const bool flat = [] { const char* e = getenv("R3DGW_FWD_FLAT"); return !(e && e[0] == '0'); }();
+#define R3DGW_FWD_LAUNCH(WC, FL, CACHE)                                                                                  \
+    do {                                                                                                                \
+        R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_forward_kernel<C, WC, FL>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+        ProfScope ps(KID_BLEND_FWD, stream);                                                                            \
+        blend_forward_kernel<C, WC, FL><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, features, bg, final_T,    \
+                                                                         n_contrib, out_color, CACHE);                  \
+    } while (0)
     if (cache_mode == 1) {   // compute and record the alphas
-        R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_forward_kernel<C, true>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        ProfScope ps(KID_BLEND_FWD, stream);
-        blend_forward_kernel<C, true><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, features, bg, final_T, n_contrib,
-                                                                       out_color, alpha_cache);
+        if (flat) R3DGW_FWD_LAUNCH(true, true, alpha_cache); else R3DGW_FWD_LAUNCH(true, false, alpha_cache);
     } else {
-        R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_forward_kernel<C, false>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        ProfScope ps(KID_BLEND_FWD, stream);
-        blend_forward_kernel<C, false><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, features, bg, final_T, n_contrib,
-                                                                        out_color, nullptr);
+        if (flat) R3DGW_FWD_LAUNCH(false, true, nullptr); else R3DGW_FWD_LAUNCH(false, false, nullptr);
     }
+#undef R3DGW_FWD_LAUNCH
     R3DGW_LAUNCH_CHECK();
     return 0;
 }
@@ -1115,6 +1148,7 @@ static int launch_backward(dim3 grid, const uint2* ranges, const float4* A, cons
 constexpr int BWDG_BATCH = 64;
 constexpr int BWDG_QROWS = 16;
 constexpr int BWDG_DEPTH = 8;
+constexpr int BWDG_MAX_C = 16;
 template <int C>
 struct BwdGeoCachedSmem {
     float4 A[2][BWDG_BATCH];
@@ -1126,11 +1160,22 @@ struct BwdGeoCachedSmem {
     uint64_t bar[2];
 };
 
+// Where each of the pass's C channels lives: the deferred pass covers several blend calls, whose features / forward
+// images / pixel gradients / backgrounds are separate tensors - the table addresses them in place (no concatenation
+// copies: 0.17 ms of torch.cat per step at config B).  feat[ch] already points at the channel's column of its call's
+// [P, c_call] matrix (row stride feat_stride[ch] floats); dpix / out point at the channel's [H, W] plane.
+struct BwdGeoChannels {
+    const float* feat[BWDG_MAX_C];
+    const float* dpix[BWDG_MAX_C];
+    const float* out[BWDG_MAX_C];
+    const float* bg[BWDG_MAX_C];
+    int feat_stride[BWDG_MAX_C];
+};
+
 template <int C>
 __global__ void __launch_bounds__(TILE_PIX, 4) blend_backward_geometry_cached_kernel(
     const uint2* __restrict__ ranges, const float4* __restrict__ splatA, const float4* __restrict__ splatB, int W, int H,
-    const float* __restrict__ features, const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
-    const float* __restrict__ out_images, const float* __restrict__ bg_color, const float* __restrict__ dL_dpixels,
+    const __grid_constant__ BwdGeoChannels chn, const uint32_t* __restrict__ n_contrib, const float* __restrict__ alpha_cache,
     float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic2D, float* __restrict__ dL_dopacity) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     BwdGeoCachedSmem<C>& s = *reinterpret_cast<BwdGeoCachedSmem<C>*>(smem_raw);
@@ -1171,12 +1216,12 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_backward_geometry_cached_ke
 #pragma unroll
     for (int q = 0; q < CP / 2; ++q) {
         const int c0 = 2 * q, c1 = 2 * q + 1;
-        dpix[q].x = (inside && c0 < C) ? dL_dpixels[(size_t)c0 * H * W + pix_id] : 0.f;
-        dpix[q].y = (inside && c1 < C) ? dL_dpixels[(size_t)c1 * H * W + pix_id] : 0.f;
-        if (inside && c0 < C) Sb = fmaf(out_images[(size_t)c0 * H * W + pix_id], dpix[q].x, Sb);
-        if (inside && c1 < C) Sb = fmaf(out_images[(size_t)c1 * H * W + pix_id], dpix[q].y, Sb);
-        if (c0 < C) bg_dot = fmaf(bg_color[c0], dpix[q].x, bg_dot);
-        if (c1 < C) bg_dot = fmaf(bg_color[c1], dpix[q].y, bg_dot);
+        dpix[q].x = (inside && c0 < C) ? chn.dpix[c0 < C ? c0 : 0][pix_id] : 0.f;
+        dpix[q].y = (inside && c1 < C) ? chn.dpix[c1 < C ? c1 : 0][pix_id] : 0.f;
+        if (inside && c0 < C) Sb = fmaf(chn.out[c0 < C ? c0 : 0][pix_id], dpix[q].x, Sb);
+        if (inside && c1 < C) Sb = fmaf(chn.out[c1 < C ? c1 : 0][pix_id], dpix[q].y, Sb);
+        if (c0 < C) bg_dot = fmaf(*chn.bg[c0 < C ? c0 : 0], dpix[q].x, bg_dot);
+        if (c1 < C) bg_dot = fmaf(*chn.bg[c1 < C ? c1 : 0], dpix[q].y, bg_dot);
     }
     const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
     float T = 1.0f, prefix = 0.f;
@@ -1188,10 +1233,10 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_backward_geometry_cached_ke
         mbar_wait(&s.bar[buf], (uint32_t)(i >> 1) & 1u);
         if ((int)tid < cnt) {
             const uint32_t id = __float_as_uint(s.B[buf][tid].w);
-            const float* f = features + (size_t)id * C;
             float fv[CP];
 #pragma unroll
-            for (int ch = 0; ch < CP; ++ch) fv[ch] = ch < C ? f[ch] : 0.f;
+            for (int ch = 0; ch < CP; ++ch)
+                fv[ch] = ch < C ? chn.feat[ch < C ? ch : 0][(size_t)id * chn.feat_stride[ch < C ? ch : 0]] : 0.f;
 #pragma unroll
             for (int q = 0; q < CP / 4; ++q)
                 s.feat[buf][tid * (CP / 4) + q] = make_float4(fv[4 * q], fv[4 * q + 1], fv[4 * q + 2], fv[4 * q + 3]);
@@ -1318,27 +1363,44 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_backward_geometry_cached_ke
 
 template <int C>
 static int launch_backward_geometry_cached(dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W, int H,
-                                           const float* features, const uint32_t* n_contrib, const float* alpha_cache,
-                                           const float* out_images, const float* bg, const float* dL_dpix, float* dL_dmean2D,
-                                           float* dL_dconic, float* dL_dopacity, cudaStream_t stream) {
+                                           const BwdGeoChannels& chn, const uint32_t* n_contrib, const float* alpha_cache,
+                                           float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, cudaStream_t stream) {
     const int smem = (int)sizeof(BwdGeoCachedSmem<C>);
     R3DGW_CUDA_TRY(cudaFuncSetAttribute((blend_backward_geometry_cached_kernel<C>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     {
         ProfScope ps(KID_BLEND_BWD_GEOM, stream);
-        blend_backward_geometry_cached_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, features, n_contrib, alpha_cache,
-                                                                                  out_images, bg, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity);
+        blend_backward_geometry_cached_kernel<C><<<grid, TILE_PIX, smem, stream>>>(ranges, A, B, W, H, chn, n_contrib, alpha_cache,
+                                                                                  dL_dmean2D, dL_dconic, dL_dopacity);
     }
     R3DGW_LAUNCH_CHECK();
     return 0;
 }
 
-int blend_backward_geometry_cached_dispatch(int C, dim3 grid, const uint2* ranges, const float4* A, const float4* B, int W,
-                                            int H, const float* features, const uint32_t* n_contrib,
-                                            const float* alpha_cache, const float* out_images, const float* bg,
-                                            const float* dL_dpix, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
-                                            cudaStream_t stream) {
+// n_calls blend calls of channels[i] channels each (sum = an instantiated total); features[i] f32[P, channels[i]],
+// out_images[i] / dL_dpix[i] f32[channels[i], H, W], bg[i] f32[channels[i]] - all device pointers, in host arrays
+int blend_backward_geometry_cached_dispatch(int n_calls, const int* channels, dim3 grid, const uint2* ranges, const float4* A,
+                                            const float4* B, int W, int H, const float* const* features,
+                                            const uint32_t* n_contrib, const float* alpha_cache,
+                                            const float* const* out_images, const float* const* bg,
+                                            const float* const* dL_dpix, float* dL_dmean2D, float* dL_dconic,
+                                            float* dL_dopacity, cudaStream_t stream) {
+    BwdGeoChannels chn;
+    memset(&chn, 0, sizeof(chn));
+    int C = 0;
+    const size_t plane = (size_t)H * W;
+    for (int i = 0; i < n_calls; ++i) {
+        const int c = channels[i];
+        if (c <= 0 || C + c > BWDG_MAX_C || !features[i] || !out_images[i] || !bg[i] || !dL_dpix[i]) return R3DGW_ERR_BAD_ARG;
+        for (int k = 0; k < c; ++k, ++C) {
+            chn.feat[C] = features[i] + k;
+            chn.feat_stride[C] = c;
+            chn.dpix[C] = dL_dpix[i] + (size_t)k * plane;
+            chn.out[C] = out_images[i] + (size_t)k * plane;
+            chn.bg[C] = bg[i] + k;
+        }
+    }
     switch (C) {
-#define R3DGW_BWDG_CASE(N) case N: return launch_backward_geometry_cached<N>(grid, ranges, A, B, W, H, features, n_contrib, alpha_cache, out_images, bg, dL_dpix, dL_dmean2D, dL_dconic, dL_dopacity, stream);
+#define R3DGW_BWDG_CASE(N) case N: return launch_backward_geometry_cached<N>(grid, ranges, A, B, W, H, chn, n_contrib, alpha_cache, dL_dmean2D, dL_dconic, dL_dopacity, stream);
         R3DGW_BWDG_CASE(3) R3DGW_BWDG_CASE(4) R3DGW_BWDG_CASE(6) R3DGW_BWDG_CASE(8) R3DGW_BWDG_CASE(9) R3DGW_BWDG_CASE(12)
         R3DGW_BWDG_CASE(15) R3DGW_BWDG_CASE(16)
 #undef R3DGW_BWDG_CASE

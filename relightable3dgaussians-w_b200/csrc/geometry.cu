@@ -440,6 +440,67 @@ __device__ __forceinline__ bool splat_may_touch(float cx, float cy, float A, flo
 // (1 % safety margin), so the blend can skip the exp without changing any decision.  Its low 8 mantissa bits
 // (a perturbation < 2e-4, inside the margin) carry the cull mask: bit w set <=> the splat can reach the 8x4
 // footprint of warp w of its tile (warp w covers columns (w&1)*8.., rows (w>>1)*4.. - blend.cu tile_pixel).
+// The same test for all eight footprints of a tile at once.  On a line x = X the quadratic is
+// q(X, t) = (A - B^2/C) X^2 + C (t - y*)^2 with y* = -(B/C) X, so the clamped 1-D minimum over t in [y0, y1] is the
+// line's base term plus C times the squared distance from y* to the interval; the eight boxes share 4 vertical lines
+// (x offsets of columns 0, 7, 8, 15) with 4 row intervals each and 8 horizontal lines (rows 0, 3, 4, 7, ...) with 2
+// column intervals each: 32 five-instruction evaluations + 12 line set-ups instead of 8 x 4 independent edge
+// minimisations (K3 was FP32-issue bound on them: 711 -> ~300 instructions per duplicate).
+// Conservative like splat_may_touch: absolute margin 2e-3 on the power, relative 2e-5 on q, plus 1e-6 of the largest
+// cancelling terms (A X^2, C Y^2 at the far corner of the tile); A <= 0, C <= 0 or NaN keeps every footprint.
+__device__ __forceinline__ uint32_t tile_cull_mask(float cx, float cy, float A, float B, float C, float thr, float tx,
+                                                   float ty) {
+    if (!(A > 0.f) || !(C > 0.f) || !(B == B)) return 0xFFu;
+    float invC, invA;      // approximate reciprocals (1 ulp-ish): y*, x* and the base terms move by ~1e-7 relative, inside the guard
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(invC) : "f"(C));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(invA) : "f"(A));
+    const float nBiC = -B * invC, nBiA = -B * invA;
+    const float Dx = fmaf(B, nBiC, A), Dy = fmaf(B, nBiA, C);     // A - B^2/C, C - B^2/A
+    // offsets d = centre - pixel of the 4 column lines / 8 row lines (descending pixel = ascending offset order)
+    const float X0 = cx - tx, Y0 = cy - ty;
+    const float ax = fmaxf(fabsf(X0), fabsf(X0 - 15.f)), ay = fmaxf(fabsf(Y0), fabsf(Y0 - 15.f));
+    // cull iff q_min (1 - 2e-5) > 2 (2e-3 - thr) + guard   <=>   -q_min/2 < thr - (2e-3 + 1e-5 q_min) - guard/2
+    const float qcut = fmaf(2.f, 2e-3f - thr, 1e-6f * fmaf(A * ax, ax, C * ay * ay));
+    // column lines (pixels 0, 7, 8, 15): y* and base term, kept across the four footprint rows
+    float ysl[4], basel[4];
+#pragma unroll
+    for (int l = 0; l < 4; ++l) {
+        const float X = X0 - (float)((l >> 1) * 8 + (l & 1) * 7);
+        ysl[l] = nBiC * X;
+        basel[l] = Dx * X * X;
+    }
+    const bool inx0 = (X0 - 7.f <= 0.f) && (X0 >= 0.f), inx1 = (X0 - 15.f <= 0.f) && (X0 - 8.f >= 0.f);
+    uint32_t mask = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {          // footprint row k: pixels 4k .. 4k+3, both footprints of the row
+        const float y1 = Y0 - (float)(4 * k), y0 = y1 - 3.f;
+        float qv[4];
+#pragma unroll
+        for (int l = 0; l < 4; ++l) {
+            const float e = fminf(fmaxf(ysl[l], y0), y1) - ysl[l];
+            qv[l] = fmaf(C * e, e, basel[l]);
+        }
+        float qh[2] = {3.0e38f, 3.0e38f};   // min over the row's two lines (pixels 4k and 4k+3), per column interval
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const float Y = r ? y0 : y1;
+            const float xs = nBiA * Y, base = Dy * Y * Y;
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const float x1 = X0 - (float)(8 * b), x0 = x1 - 7.f;
+                const float e = fminf(fmaxf(xs, x0), x1) - xs;
+                qh[b] = fminf(qh[b], fmaf(A * e, e, base));
+            }
+        }
+        const bool iny = (y0 <= 0.f) && (y1 >= 0.f);
+        const float q0 = fminf(fminf(qv[0], qv[1]), qh[0]), q1 = fminf(fminf(qv[2], qv[3]), qh[1]);
+        if ((inx0 && iny) || !(q0 * (1.f - 2e-5f) > qcut)) mask |= 1u << (2 * k);
+        if ((inx1 && iny) || !(q1 * (1.f - 2e-5f) > qcut)) mask |= 1u << (2 * k + 1);
+    }
+    return mask;
+}
+
+template <bool CULL_V2>
 __global__ void __launch_bounds__(256) ranges_gather_kernel(
     int L, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
@@ -465,10 +526,14 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(
     if (!(co.w == co.w)) thr = -1e30f;   // NaN opacity: never skip, let the exact path decide
     const float tx = (float)((currtile % gx) * TILE_X), ty = (float)((currtile / gx) * TILE_Y);
     uint32_t mask = 0;
+    if constexpr (CULL_V2) {
+        mask = tile_cull_mask(xy.x, xy.y, co.x, co.y, co.z, thr, tx, ty);
+    } else {
 #pragma unroll
-    for (int w = 0; w < 8; ++w) {
-        const float rx0 = tx + (float)((w & 1) * 8), ry0 = ty + (float)((w >> 1) * 4);
-        if (splat_may_touch(xy.x, xy.y, co.x, co.y, co.z, thr, rx0, rx0 + 7.f, ry0, ry0 + 3.f)) mask |= 1u << w;
+        for (int w = 0; w < 8; ++w) {
+            const float rx0 = tx + (float)((w & 1) * 8), ry0 = ty + (float)((w >> 1) * 4);
+            if (splat_may_touch(xy.x, xy.y, co.x, co.y, co.z, thr, rx0, rx0 + 7.f, ry0, ry0 + 3.f)) mask |= 1u << w;
+        }
     }
     const float thr_packed = __uint_as_float((__float_as_uint(thr) & ~0xFFu) | mask);
     splatA[idx] = make_float4(xy.x, xy.y, co.x, co.y);

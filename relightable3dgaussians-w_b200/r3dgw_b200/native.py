@@ -35,6 +35,7 @@ SYMBOLS = [
     "r3dgw_gaussian_regularisers_backward", "r3dgw_normal_tail_forward", "r3dgw_normal_tail_backward",
     "r3dgw_normal_loss_forward", "r3dgw_normal_loss_backward", "r3dgw_blend_backward_geometry_cached",
     "r3dgw_gaussian_regularisers_noalloc_max_gaussians", "r3dgw_gaussian_regularisers_forward_noalloc",
+    "r3dgw_blend_backward_geometry_cached_calls",
 ]
 
 
@@ -146,6 +147,10 @@ def lib():
     L.r3dgw_blend_forward_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, vp, vp, ci, vp]
     L.r3dgw_blend_backward_color_cached.argtypes = [ci, ci, ci, cam, vp, vp, vp, vp, vp, ci, vp]
     L.r3dgw_blend_backward_geometry_cached.argtypes = [ci, ci, ci, cam] + [vp] * 11
+    # (P, R, n_calls, channels*, cam, binning, image, alpha_cache, features**, out_images**, backgrounds**, dL_dpixels**, ...)
+    L.r3dgw_blend_backward_geometry_cached_calls.argtypes = [ci, ci, ci, ctypes.POINTER(ci), cam, vp, vp, vp,
+                                                             ctypes.POINTER(vp), ctypes.POINTER(vp), ctypes.POINTER(vp),
+                                                             ctypes.POINTER(vp), vp, vp, vp, vp]
     L.r3dgw_materialize_sorted_keys.argtypes = [ci, ci, ci, ci, vp, vp, vp]
     L.r3dgw_alpha_cache_bytes.argtypes = [ci]
     L.r3dgw_alpha_cache_bytes.restype = ctypes.c_size_t

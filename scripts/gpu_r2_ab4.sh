@@ -1,0 +1,12 @@
+#!/bin/bash
+# A/B: shared-line footprint cull in K3 (R3DGW_CULL_V2) and in-place deferred geometry pass (R3DGW_BWDG_IN_PLACE)
+cd "$GRAFT_REPO_ROOT"; mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+run() {
+  echo "== $*"
+  env "$@" python bench.py --steps 20 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['ms_per_step'],3), round(d['e2e']['ms_per_step'],3), 'fused', round(d['fused_single_pass']['ms_per_step'],3), 'u1', d['u1_raster_call'], 'rows', d['scene'].get('alpha_cache_rows'), {k:round(v['ms_per_step'],3) for k,v in d['kernels'].items() if 'blend' in k or 'ranges' in k})"
+}
+run R3DGW_CULL_V2=0 R3DGW_BWDG_IN_PLACE=0
+run R3DGW_CULL_V2=1 R3DGW_BWDG_IN_PLACE=0
+run R3DGW_CULL_V2=1 R3DGW_BWDG_IN_PLACE=1
