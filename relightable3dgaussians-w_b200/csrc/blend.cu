@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     const uint32_t pix_id = W * pix.y + pix.x;
     const float2 pixf = {(float)pix.x, (float)pix.y};
     const bool inside = pix.x < (unsigned)W && pix.y < (unsigned)H;
-    bool done = !inside;
+    int done = inside ? 0 : 1;     // int, not bool: a byte-typed flag costs PRMT / SEL pairs per row
     const unsigned lane = tid & 31, warp = tid >> 5;
 
     const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
     constexpr int CP = ChanPad<C>::CP;
     float T = 1.0f;
     uint32_t last_contributor = 0;
+    uint32_t last_row = 0xFFFFFFFFu;   // FLAT: this round's last taken list slot
     // alpha-cache layout: tile t owns rows [range.x * 8, range.y * 8) of 32 floats; warp w's rows are the `total`
     // rows from range.x * 8 + w * total, filled in the order the warp walks its survivors (row k = its k-th
     // surviving list entry): every replay streams one contiguous run per warp
@@ -191,10 +192,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                     const float alpha = min(0.99f, b.y * exp(power));
                     const float test_T = T * (1 - alpha);
                     // !(x > 0) && !(x < thr) keeps the branchy form's NaN behaviour (a NaN power goes on to alpha)
-                    const bool cand = !done & !(power > 0.0f) & !(power < b.z) & !(alpha < 1.0f / 255.0f);
+                    const bool cand = (done == 0) & !(power > 0.0f) & !(power < b.z) & !(alpha < 1.0f / 255.0f);
                     const bool stop = cand & (test_T < 0.0001f);
                     const bool take = cand & !stop;
-                    done |= stop;
+                    if (stop) done = 1;
                     const float w = take ? alpha * T : 0.f;
                     const float2 w2 = make_float2(w, w);
                     if (take) {
@@ -205,7 +206,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                             Cacc[2 * q + 1] = __ffma2_rn(make_float2(f.z, f.w), w2, Cacc[2 * q + 1]);
                         }
                         T = test_T;
-                        last_contributor = base + (uint32_t)j + 1u;
+                        last_row = (uint32_t)j;          // resolved to base + j + 1 once per round, below
                         a_eff = alpha;
                     }
                 } else if (!done) {
@@ -220,7 +221,7 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                         if (alpha < 1.0f / 255.0f) break;
                         const float test_T = T * (1 - alpha);
                         if (test_T < 0.0001f) {
-                            done = true;
+                            done = 1;
                             break;
                         }
                         const float w = alpha * T;   // (f*alpha)*T in the reference: differs by <= 1 ulp per term
@@ -242,6 +243,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_forward_kernel(
                 }
             }
             if (__all_sync(0xffffffffu, done)) break;
+        }
+        if constexpr (FLAT) {
+            if (last_row != 0xFFFFFFFFu) last_contributor = base + last_row + 1u;
+            last_row = 0xFFFFFFFFu;
         }
     }
 
