@@ -157,9 +157,15 @@ class _PreshadeFn(torch.autograd.Function):
             gptrs = [b, b + 12, b + 24, b + 36, b + 48]
             keep = g
         else:
-            keep = [torch.zeros(P, 3, dtype=torch.float32, device=dev) if (x is None and k == 0) else
-                    (None if x is None else _c(x)) for k, x in enumerate(grads)]
-            stride = 3
+            # the blend backward hands out its 16-byte padded gradient rows as [P,3] views of [P,4] buffers: read them
+            # in place through the row stride (five .contiguous() copies per step otherwise)
+            live = [x for x in grads if x is not None]
+            stride = int(live[0].stride(0)) if live and live[0].dim() == 2 else 3
+            if not (stride >= 3 and all(x.dim() == 2 and x.dtype == torch.float32 and x.stride(1) == 1 and
+                                        x.stride(0) == stride and x.shape == (P, 3) for x in live)):
+                stride = 3
+            keep = [torch.zeros(P, stride, dtype=torch.float32, device=dev) if (x is None and k == 0) else
+                    (None if x is None else (x if stride != 3 else _c(x))) for k, x in enumerate(grads)]
             gptrs = [_ptr(x) for x in keep]
         # one zero-filled block for every per-Gaussian gradient + the SH gradients (accumulated with atomics)
         n_fg = int(alb.shape[0])
