@@ -839,7 +839,8 @@ def main():
             if dist is not None:
                 dist.all_reduce(st_f.flat_grads())
         nfz = max(5, args.steps // 2)
-        ms_f = timed_steps(torch, step_fused, nfz, 4, flush, dist) / nfz
+        ms_f = timed_steps(torch, step_fused, nfz, 8, flush, dist) / nfz
+        print("fused step ms:", [round(x, 2) for x in LAST_STEP_MS], file=sys.stderr)
         line["fused_single_pass"] = {"value": world * 1e3 / ms_f, "unit": UNIT, "ms_per_step": ms_f,
                                      "api": "r3dgw_b200.render.render_fused (SURVEY 8f N1/N2), same loss and gradients"}
         del st_f

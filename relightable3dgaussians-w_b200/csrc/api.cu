@@ -67,6 +67,56 @@ int sort_num_passes(int end_bit);
 
 static inline int pre_blocks(int P) { return (P + PRE_THREADS - 1) / PRE_THREADS; }
 
+// ---- early read-back of R ------------------------------------------------------------------------------
+// R (num_rendered) is final when preprocess_scan_kernel ends, but the depth sort is enqueued behind it on the caller's
+// stream, and a read-back ordered on that stream only returns once the sort has drained - the host then allocates
+// the binning buffers and enqueues duplicate / sort / ranges / blend into an idle GPU (~30 us per geometry).  The
+// 4-byte copy therefore runs on a private non-blocking stream behind an event recorded right after the preprocess
+// launch, into pinned memory: the host learns R while the sort still runs and the next kernels queue up behind it.
+// One side stream per device and a pool of (event, pinned word) slots, created on first use; a call owns its slot from
+// the record to the read.  R3DGW_EARLY_R=0 restores the read-back on the caller's stream.
+namespace {
+struct EarlyRSlot { cudaEvent_t ev = nullptr; uint32_t* pinned = nullptr; };
+struct EarlyRDev { cudaStream_t side = nullptr; std::vector<EarlyRSlot> free_slots; };
+EarlyRDev g_early_r[64];
+std::mutex g_early_r_mu;
+}  // namespace
+
+// takes a (event, pinned word) slot of the current device and records "preprocess done" on the caller's stream;
+// call right after the preprocess launch.  Every call owns its slot until read_R_early returns it, so concurrent
+// callers (other host threads / streams) never wait on each other's events.
+static int mark_R_ready(cudaStream_t stream, EarlyRSlot* slot, int* dev_out) {
+    int dev = -1;
+    R3DGW_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return R3DGW_ERR_UNSUPPORTED;
+    *dev_out = dev;
+    {
+        std::lock_guard<std::mutex> lk(g_early_r_mu);
+        EarlyRDev& d = g_early_r[dev];
+        if (!d.side) R3DGW_CUDA_TRY(cudaStreamCreateWithFlags(&d.side, cudaStreamNonBlocking));
+        if (!d.free_slots.empty()) { *slot = d.free_slots.back(); d.free_slots.pop_back(); }
+    }
+    if (!slot->ev) {
+        R3DGW_CUDA_TRY(cudaEventCreateWithFlags(&slot->ev, cudaEventDisableTiming));
+        R3DGW_CUDA_TRY(cudaHostAlloc((void**)&slot->pinned, sizeof(uint32_t), cudaHostAllocDefault));
+    }
+    R3DGW_CUDA_TRY(cudaEventRecord(slot->ev, stream));
+    return 0;
+}
+
+static int read_R_early(int dev, EarlyRSlot slot, const uint32_t* total_out, uint32_t* R) {
+    cudaStream_t side;
+    { std::lock_guard<std::mutex> lk(g_early_r_mu); side = g_early_r[dev].side; }
+    cudaError_t err = cudaStreamWaitEvent(side, slot.ev, 0);
+    if (err == cudaSuccess) err = cudaMemcpyAsync(slot.pinned, total_out, sizeof(uint32_t), cudaMemcpyDeviceToHost, side);
+    // the copy is the last thing queued on the side stream by this thread; a later copy of another thread may also be
+    // waited for here (harmless)
+    if (err == cudaSuccess) err = cudaStreamSynchronize(side);
+    if (err == cudaSuccess) *R = *slot.pinned;
+    { std::lock_guard<std::mutex> lk(g_early_r_mu); g_early_r[dev].free_slots.push_back(slot); }
+    return (int)err;
+}
+
 // depth-first binning scratch inside the geometry buffer: keys | keys_alt | ids | ids_alt | radix workspace |
 // K2' look-back states (+ ticket)
 struct DepthSortLayout { size_t keys, keys_alt, ids, ids_alt, ws, dup_state, total; };
@@ -234,6 +284,9 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
             preprocess_scan_kernel<<<blocks, PRE_THREADS, 0, stream>>>(pp);
         }
         R3DGW_LAUNCH_CHECK();
+        static const bool early_r = [] { const char* e = getenv("R3DGW_EARLY_R"); return !(e && e[0] == '0'); }();
+        EarlyRSlot r_slot; int r_dev = -1;
+        if (early_r) { const int rc = mark_R_ready(stream, &r_slot, &r_dev); if (rc) return rc; }
         // depth-first binning, step 1: stable sort of the P Gaussians by depth bits - enqueued BEFORE the read-back of
         // R so that it runs while the host waits
         {
@@ -257,8 +310,13 @@ int r3dgw_geometry_forward(r3dgw_alloc_fn geom_alloc, void* geom_ctx, r3dgw_allo
             }
         }
         // the one blocking read-back of the path (reference: rasterizer_impl.cu:281)
-        R3DGW_CUDA_TRY(cudaMemcpyAsync(&R, pp.total_out, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-        R3DGW_CUDA_TRY(cudaStreamSynchronize(stream));
+        if (early_r) {
+            const int rc = read_R_early(r_dev, r_slot, pp.total_out, &R);
+            if (rc) return rc;
+        } else {
+            R3DGW_CUDA_TRY(cudaMemcpyAsync(&R, pp.total_out, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+            R3DGW_CUDA_TRY(cudaStreamSynchronize(stream));
+        }
         if (R > (uint32_t)INT_MAX) return R3DGW_ERR_OVERFLOW;
     }
 

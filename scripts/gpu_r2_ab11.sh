@@ -1,0 +1,12 @@
+#!/bin/bash
+cd "$GRAFT_REPO_ROOT"; mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
+run() {
+  echo "== $*"
+  env "$@" python bench.py --steps 20 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['ms_per_step'],3), round(d['e2e']['ms_per_step'],3), 'fused', round(d['fused_single_pass']['ms_per_step'],3), 'u1', d['u1_raster_call'], 'fps', round(d['fps_fwd'],1), round(d['fps_fwd_relit_same_view'],1))"
+}
+run R3DGW_EARLY_R=0
+run R3DGW_EARLY_R=1
+run R3DGW_EARLY_R=0
+run R3DGW_EARLY_R=1
