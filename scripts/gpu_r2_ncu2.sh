@@ -29,3 +29,6 @@ for k in blend_backward_geometry_cached_kernel shade_backward_kernel blend_backw
   ncu -i gpurun_out/prof_u2_r02c.ncu-rep --page source --csv --kernel-name-base demangled -k regex:$k -c 1 > gpurun_out/src_$k.csv 2>/dev/null
   python scripts/ncu_src_summary.py gpurun_out/src_$k.csv 0.02 > gpurun_out/src_$k.txt 2>&1; head -30 gpurun_out/src_$k.txt
 done
+python scripts/diag_timeline.py > gpurun_out/timeline.txt 2>&1
+# the report itself is > 64 MiB (gpurun_out/ would not travel back): keep the summaries, drop the report
+rm -f gpurun_out/prof_u2_r02c.ncu-rep gpurun_out/ncu_u2_raw.csv gpurun_out/src_*.csv
