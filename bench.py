@@ -398,8 +398,16 @@ def timed_steps(torch, fn, steps, warmup, flush_buf, dist=None, sampler=None):
         a.record()
         fn()
         b.record()
-        if sampler is not None and RANK0_SAMPLES and (SAMPLE_EVERY_STEP or (len(sampler.samples) < 6 and k % 4 == 1)):
-            sampler.sample()      # GPU still busy with the step just enqueued; outside every event pair
+        if sampler is not None and (SAMPLE_EVERY_STEP or (k % 4 == 1 and k // 4 < 6)):
+            if RANK0_SAMPLES:
+                sampler.sample()      # GPU still busy with the step just enqueued; outside every event pair
+            if dist is not None:
+                # An NVML query costs rank 0's host 3 ms as a rule and 150 ms now and then.  Without this barrier the
+                # other ranks enqueue their next step at once and its event pair then spans the wait for rank 0 inside
+                # the all-reduce: rank 0's own step list stays flat while every other rank reports one 9-150 ms step,
+                # and the MAX over ranks charges the query to the job (N = 4 on an 8-GPU box: 12.8 instead of 5.45
+                # ms/step).  With it every rank absorbs the query between its event pairs, like rank 0 does.
+                dist.barrier()
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
