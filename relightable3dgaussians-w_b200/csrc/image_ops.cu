@@ -18,6 +18,7 @@ constexpr int WIN = 11, HALO = 5;          // window_size = 11, padding = 5 (los
 constexpr int IMG_IN = IMG_T + 2 * HALO;   // 42
 constexpr int IMG_THREADS = 256;
 constexpr int IMG_WARPS = IMG_THREADS / 32;
+constexpr int IMG_RB = 4;                  // outputs per thread per separable pass (register blocking)
 
 // gaussian(11, 1.5) / sum, exactly the float32 values torch produces for loss_utils.py:41-44
 // (exp evaluated in double by Python, rounded to f32 by torch.Tensor, divided by the f32 sum)
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(IMG_THREADS) ssim_l1_forward_kernel(
     float* __restrict__ partials) {
     __shared__ float s1[IMG_IN][IMG_IN + 1];
     __shared__ float s2[IMG_IN][IMG_IN + 1];
-    __shared__ float hs[5][IMG_IN][IMG_T];
+    __shared__ __align__(16) float hs[5][IMG_IN][IMG_T];
     __shared__ float red[3][IMG_WARPS];
     const int tid = threadIdx.x, c = blockIdx.z;
     const int x0 = blockIdx.x * IMG_T, y0 = blockIdx.y * IMG_T;
@@ -71,40 +72,64 @@ __global__ void __launch_bounds__(IMG_THREADS) ssim_l1_forward_kernel(
         s2[r][q] = in ? p2[(size_t)y * W + x] : 0.f;
     }
     __syncthreads();
-    // horizontal pass: 42 rows x 32 columns, 5 moments
-    for (int i = tid; i < IMG_IN * IMG_T; i += IMG_THREADS) {
-        const int r = i >> 5, q = i & 31;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+    // horizontal pass, register-blocked: one item = IMG_RB consecutive outputs of one row, fed from WIN + IMG_RB - 1
+    // loads per image instead of WIN per output (the pass was shared-memory-bound: ncu LSU pipe 70 %); a warp takes
+    // 8 column groups x 4 rows (row stride 43 words: 32 distinct banks); per output the same operations in the same
+    // order as the one-output-per-thread form
+    for (int i = tid; i < IMG_IN * (IMG_T / IMG_RB); i += IMG_THREADS) {
+        const int r = i / (IMG_T / IMG_RB), q0 = (i - r * (IMG_T / IMG_RB)) * IMG_RB;
+        float xs[WIN + IMG_RB - 1], ys[WIN + IMG_RB - 1];
 #pragma unroll
-        for (int k = 0; k < WIN; ++k) {
-            const float x = s1[r][q + k], y = s2[r][q + k];
-            const float wx = win.w[k] * x, wy = win.w[k] * y;
-            a0 += wx;
-            a1 += wy;
-            a2 = fmaf(wx, x, a2);
-            a3 = fmaf(wy, y, a3);
-            a4 = fmaf(wx, y, a4);
+        for (int t = 0; t < WIN + IMG_RB - 1; ++t) { xs[t] = s1[r][q0 + t]; ys[t] = s2[r][q0 + t]; }
+        float o0[IMG_RB], o1[IMG_RB], o2[IMG_RB], o3[IMG_RB], o4[IMG_RB];
+#pragma unroll
+        for (int o = 0; o < IMG_RB; ++o) {
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+#pragma unroll
+            for (int k = 0; k < WIN; ++k) {
+                const float x = xs[o + k], y = ys[o + k];
+                const float wx = win.w[k] * x, wy = win.w[k] * y;
+                a0 += wx;
+                a1 += wy;
+                a2 = fmaf(wx, x, a2);
+                a3 = fmaf(wy, y, a3);
+                a4 = fmaf(wx, y, a4);
+            }
+            o0[o] = a0; o1[o] = a1; o2[o] = a2; o3[o] = a3; o4[o] = a4;
         }
-        hs[0][r][q] = a0; hs[1][r][q] = a1; hs[2][r][q] = a2; hs[3][r][q] = a3; hs[4][r][q] = a4;
+        static_assert(IMG_RB == 4, "the row writes below are one float4 per moment");
+        *reinterpret_cast<float4*>(&hs[0][r][q0]) = make_float4(o0[0], o0[1], o0[2], o0[3]);
+        *reinterpret_cast<float4*>(&hs[1][r][q0]) = make_float4(o1[0], o1[1], o1[2], o1[3]);
+        *reinterpret_cast<float4*>(&hs[2][r][q0]) = make_float4(o2[0], o2[1], o2[2], o2[3]);
+        *reinterpret_cast<float4*>(&hs[3][r][q0]) = make_float4(o3[0], o3[1], o3[2], o3[3]);
+        *reinterpret_cast<float4*>(&hs[4][r][q0]) = make_float4(o4[0], o4[1], o4[2], o4[3]);
     }
     __syncthreads();
+    // vertical pass, register-blocked the same way: a thread owns column tx and the IMG_RB consecutive rows from
+    // IMG_RB * ty (IMG_T / IMG_WARPS == IMG_RB), one moment at a time to keep the live set small
     const int tx = tid & 31, ty = tid >> 5;
+    static_assert(IMG_T / IMG_WARPS == IMG_RB, "one thread per column and IMG_RB consecutive rows");
     const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
     float accS = 0.f, accL = 0.f, accN = 0.f;
+    float mom[5][IMG_RB];
 #pragma unroll
-    for (int j = 0; j < IMG_T / IMG_WARPS; ++j) {
-        const int r = ty + IMG_WARPS * j;
-        const int y = y0 + r, x = x0 + tx;
-        float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    for (int m = 0; m < 5; ++m) {
+        float col[WIN + IMG_RB - 1];
 #pragma unroll
-        for (int k = 0; k < WIN; ++k) {
-            const float w = win.w[k];
-            mu1 = fmaf(w, hs[0][r + k][tx], mu1);
-            mu2 = fmaf(w, hs[1][r + k][tx], mu2);
-            e11 = fmaf(w, hs[2][r + k][tx], e11);
-            e22 = fmaf(w, hs[3][r + k][tx], e22);
-            e12 = fmaf(w, hs[4][r + k][tx], e12);
+        for (int t = 0; t < WIN + IMG_RB - 1; ++t) col[t] = hs[m][IMG_RB * ty + t][tx];
+#pragma unroll
+        for (int j = 0; j < IMG_RB; ++j) {
+            float a = 0.f;
+#pragma unroll
+            for (int k = 0; k < WIN; ++k) a = fmaf(win.w[k], col[j + k], a);
+            mom[m][j] = a;
         }
+    }
+#pragma unroll
+    for (int j = 0; j < IMG_RB; ++j) {
+        const int r = IMG_RB * ty + j;
+        const int y = y0 + r, x = x0 + tx;
+        const float mu1 = mom[0][j], mu2 = mom[1][j], e11 = mom[2][j], e22 = mom[3][j], e12 = mom[4][j];
         if (x < W && y < H) {
             const size_t idx = (size_t)y * W + x;
             const float m = mask ? mask[(size_t)c * mask_cstride + idx] : 1.f;
@@ -173,7 +198,7 @@ __global__ void __launch_bounds__(IMG_THREADS) ssim_l1_backward_kernel(
     const float* __restrict__ mask, size_t mask_cstride, Window win, const float* __restrict__ dmap,
     const float* __restrict__ sums, const float* __restrict__ coef, float* __restrict__ dL_dimg1) {
     __shared__ float sd[3][IMG_IN][IMG_IN + 1];
-    __shared__ float hs[3][IMG_IN][IMG_T];
+    __shared__ __align__(16) float hs[3][IMG_IN][IMG_T];
     const int tid = threadIdx.x, c = blockIdx.z;
     const int x0 = blockIdx.x * IMG_T, y0 = blockIdx.y * IMG_T;
     const size_t plane = (size_t)H * W;
@@ -186,34 +211,48 @@ __global__ void __launch_bounds__(IMG_THREADS) ssim_l1_backward_kernel(
         for (int t = 0; t < 3; ++t) sd[t][r][q] = in ? dmap[(size_t)t * C * plane + o] : 0.f;
     }
     __syncthreads();
-    for (int i = tid; i < IMG_IN * IMG_T; i += IMG_THREADS) {
-        const int r = i >> 5, q = i & 31;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+    // both passes register-blocked like the forward kernel's (IMG_RB outputs from WIN + IMG_RB - 1 loads)
+    for (int i = tid; i < IMG_IN * (IMG_T / IMG_RB); i += IMG_THREADS) {
+        const int r = i / (IMG_T / IMG_RB), q0 = (i - r * (IMG_T / IMG_RB)) * IMG_RB;
 #pragma unroll
-        for (int k = 0; k < WIN; ++k) {
-            const float w = win.w[k];
-            a0 = fmaf(w, sd[0][r][q + k], a0);
-            a1 = fmaf(w, sd[1][r][q + k], a1);
-            a2 = fmaf(w, sd[2][r][q + k], a2);
+        for (int t = 0; t < 3; ++t) {
+            float v[WIN + IMG_RB - 1];
+#pragma unroll
+            for (int u = 0; u < WIN + IMG_RB - 1; ++u) v[u] = sd[t][r][q0 + u];
+            float o[IMG_RB];
+#pragma unroll
+            for (int j = 0; j < IMG_RB; ++j) {
+                float a = 0.f;
+#pragma unroll
+                for (int k = 0; k < WIN; ++k) a = fmaf(win.w[k], v[j + k], a);
+                o[j] = a;
+            }
+            *reinterpret_cast<float4*>(&hs[t][r][q0]) = make_float4(o[0], o[1], o[2], o[3]);
         }
-        hs[0][r][q] = a0; hs[1][r][q] = a1; hs[2][r][q] = a2;
     }
     __syncthreads();
     const int tx = tid & 31, ty = tid >> 5;
     const float inv_n = sums[3];
     const float kS = coef[0] * inv_n, kL = coef[1] * inv_n;
+    float cv[3][IMG_RB];
 #pragma unroll
-    for (int j = 0; j < IMG_T / IMG_WARPS; ++j) {
-        const int r = ty + IMG_WARPS * j;
-        const int y = y0 + r, x = x0 + tx;
-        float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+    for (int t = 0; t < 3; ++t) {
+        float col[WIN + IMG_RB - 1];
 #pragma unroll
-        for (int k = 0; k < WIN; ++k) {
-            const float w = win.w[k];
-            c0 = fmaf(w, hs[0][r + k][tx], c0);
-            c1 = fmaf(w, hs[1][r + k][tx], c1);
-            c2 = fmaf(w, hs[2][r + k][tx], c2);
+        for (int u = 0; u < WIN + IMG_RB - 1; ++u) col[u] = hs[t][IMG_RB * ty + u][tx];
+#pragma unroll
+        for (int j = 0; j < IMG_RB; ++j) {
+            float a = 0.f;
+#pragma unroll
+            for (int k = 0; k < WIN; ++k) a = fmaf(win.w[k], col[j + k], a);
+            cv[t][j] = a;
         }
+    }
+#pragma unroll
+    for (int j = 0; j < IMG_RB; ++j) {
+        const int r = IMG_RB * ty + j;
+        const int y = y0 + r, x = x0 + tx;
+        const float c0 = cv[0][j], c1 = cv[1][j], c2 = cv[2][j];
         if (x < W && y < H) {
             const size_t idx = (size_t)y * W + x;
             const size_t o = (size_t)c * plane + idx;
