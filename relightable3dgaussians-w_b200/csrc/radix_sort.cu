@@ -13,8 +13,6 @@
 //                                 per-digit decoupled look-back across tiles (chained scan fused into
 //                                 the scatter pass), smem reorder, coalesced scatter.
 // HBM-bound: algorithmic bytes = n*(sizeof(K)+ (24 per pass for u64/u32 pairs)).
-#include <cstdlib>
-#include <type_traits>
 #include "common.cuh"
 
 namespace r3dgw {
@@ -110,8 +108,8 @@ struct OsSmem {
     uint32_t vals[OS_TILE];
 };
 
-template <typename KeyT, int MINB = 1>
-__global__ void __launch_bounds__(OS_THREADS, (MINB > 1 ? MINB : 0)) onesweep_pass_kernel(
+template <typename KeyT>
+__global__ void __launch_bounds__(OS_THREADS) onesweep_pass_kernel(
     const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, KeyT* __restrict__ keys_out,
     uint32_t* __restrict__ vals_out, int n, int shift, uint32_t mask,
     const uint32_t* __restrict__ digit_base,     // exclusive-scanned histogram of this pass [256]
@@ -276,30 +274,19 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
     }
     R3DGW_LAUNCH_CHECK();
 
+    static bool attr_set = false;
     const int smem = (int)sizeof(OsSmem<KeyT>);
-    // minimum resident CTAs per SM of the pass kernel, R3DGW_OS_MINB (32-bit keys only): 1 = ptxas' 80 registers / 3 CTAs,
-    // 4 = 64 registers (two spilled words) / 4 CTAs, 5 = 48 registers
-    static const int minb_env = [] { const char* e = getenv("R3DGW_OS_MINB"); return e ? atoi(e) : 1; }();
-    const int minb = sizeof(KeyT) == 4 ? minb_env : 1;
-    auto launch_pass = [&](auto tag, int p, const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout) -> int {
-        constexpr int MB = decltype(tag)::value;
-        R3DGW_CUDA_TRY(cudaFuncSetAttribute((onesweep_pass_kernel<KeyT, MB>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        onesweep_pass_kernel<KeyT, MB><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
-            kin, vin, kout, vout, n, sp.shift[p], sp.mask[p], hist + p * SORT_RADIX, counters + p,
-            status + (size_t)p * status_per_pass);
-        return 0;
-    };
+    R3DGW_CUDA_TRY(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    (void)attr_set;
 
     KeyT* kin = keys_in; KeyT* kout = keys_alt;
     uint32_t* vin = vals_in; uint32_t* vout = vals_alt;
     for (int p = 0; p < sp.n_pass; ++p) {
         {
             ProfScope ps(g_sort_prof_kid >= 0 ? g_sort_prof_kid : KID_SORT_PASS, stream);
-            int rc;
-            if (minb == 4) rc = launch_pass(std::integral_constant<int, 4>{}, p, kin, vin, kout, vout);
-            else if (minb == 5) rc = launch_pass(std::integral_constant<int, 5>{}, p, kin, vin, kout, vout);
-            else rc = launch_pass(std::integral_constant<int, 1>{}, p, kin, vin, kout, vout);
-            if (rc) return rc;
+            onesweep_pass_kernel<KeyT><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
+                kin, vin, kout, vout, n, sp.shift[p], sp.mask[p], hist + p * SORT_RADIX, counters + p,
+                status + (size_t)p * status_per_pass);
         }
         R3DGW_LAUNCH_CHECK();
         std::swap(kin, kout);
