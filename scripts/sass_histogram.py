@@ -30,6 +30,7 @@ with open(out, "w") as f:
     for k, h in hist.items():
         total.update(h)
         name = demangle(k)
+        name = re.sub(r"\((?:bool|int|unsigned int)\)", "", name)      # template-argument casts: <(bool)1> -> <1>
         name = re.sub(r"\(.*", "", name).replace("void r3dgw::", "").replace("r3dgw::", "")
         n = sum(h.values())
         f.write(f"\n== {name}  [{n} instructions]\n")
