@@ -1294,7 +1294,6 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_backward_geometry_cached_ke
                         dot2 = __ffma2_rn(make_float2(f.z, f.w), dpix[2 * q + 1], dot2);
                     }
                     const float sdot = dot2.x + dot2.y;
-                    const float4 b = s.B[buf][jj];
                     prefix = fmaf(alpha * T, sdot, prefix);
                     const float one_m = 1.f - alpha;
                     const float T_next = T * one_m;
@@ -1303,13 +1302,17 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_backward_geometry_cached_ke
                     const float bracket = (base + (uint32_t)jj + 1u == my_last) ? T_next * bg_dot : Sb - prefix;
                     const float dL_dalpha = fmaf(T, sdot, -bracket * bwd_rcp(one_m));
                     T = T_next;
-                    float G = alpha * bwd_rcp(b.y);
+                    // parked: q' = opacity * G * dL/dalpha.  Off the clamp opacity * G IS alpha, so the row walk needs
+                    // neither the splat's B entry nor a reciprocal; the common factor 1 / opacity is applied once per
+                    // (warp, splat) where the six sums are turned into gradients (it cancels in five of them)
+                    float oG = alpha;
                     if (alpha == 0.99f) {      // on the clamp: alpha no longer determines G
                         const float4 a = s.A[buf][jj];
+                        const float4 b = s.B[buf][jj];
                         const float2 d = {a.x - pixf.x, a.y - pixf.y};
-                        G = bwd_exp(-0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y);
+                        oG = b.y * bwd_exp(-0.5f * (a.z * d.x * d.x + b.x * d.y * d.y) - a.w * d.x * d.y);
                     }
-                    s.Q[warp][r][lane] = G * dL_dalpha;      // alpha == 0 (pixel did not take the splat): exactly 0
+                    s.Q[warp][r][lane] = oG * dL_dalpha;     // alpha == 0 (pixel did not take the splat): exactly 0
                 }
             }
             // ---- six moments of q over the box-local pixel coordinates, 32 / QROWS lanes per row ----
@@ -1353,12 +1356,12 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_backward_geometry_cached_ke
                     const float XX = fmaf(mx, fmaf(mx, S0, -2.f * Su), Suu);
                     const float YY = fmaf(my, fmaf(my, S0, -2.f * Sv), Svv);
                     const float XY = fmaf(mx, fmaf(my, S0, -Sv), fmaf(-my, Su, Suv));
-                    const float o = b.y, ho = -0.5f * o;
+                    // the sums carry opacity * G: dL/dG * G = opacity * q cancels the factor, dL/dopacity = sum(q) keeps it
                     const uint32_t id = __float_as_uint(b.w);
-                    atomicAdd(dL_dmean2D + (size_t)id * 3, -o * (a.z * X1 + a.w * Y1) * ddelx_dx);
-                    atomicAdd(dL_dmean2D + (size_t)id * 3 + 1, -o * (b.x * Y1 + a.w * X1) * ddely_dy);
-                    red_add_v4(dL_dconic2D + (size_t)id * 4, ho * XX, ho * XY, 0.f, ho * YY);
-                    atomicAdd(dL_dopacity + id, S0);
+                    atomicAdd(dL_dmean2D + (size_t)id * 3, -(a.z * X1 + a.w * Y1) * ddelx_dx);
+                    atomicAdd(dL_dmean2D + (size_t)id * 3 + 1, -(b.x * Y1 + a.w * X1) * ddely_dy);
+                    red_add_v4(dL_dconic2D + (size_t)id * 4, -0.5f * XX, -0.5f * XY, 0.f, -0.5f * YY);
+                    atomicAdd(dL_dopacity + id, S0 * bwd_rcp(b.y));
                 }
             }
             __syncwarp();   // Q is rewritten by the next block
