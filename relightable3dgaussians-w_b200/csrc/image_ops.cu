@@ -55,9 +55,12 @@ __global__ void __launch_bounds__(IMG_THREADS) ssim_l1_forward_kernel(
     int C, int H, int W, const float* __restrict__ img1, const float* __restrict__ img2,
     const float* __restrict__ mask, size_t mask_cstride, Window win, float* __restrict__ dmap,
     float* __restrict__ partials) {
-    __shared__ float s1[IMG_IN][IMG_IN + 1];
-    __shared__ float s2[IMG_IN][IMG_IN + 1];
-    __shared__ __align__(16) float hs[5][IMG_IN][IMG_T];
+    // the two images interleaved (x, y) and the five horizontal moments as (mu1, mu2, E[xx], E[yy]) + E[xy]: one 8-byte /
+    // 16-byte shared load feeds packed FP32 pairs (FMUL2 / FADD2 / FFMA2: IEEE per lane, the same operations in the same
+    // order per output as the scalar form - the kernel is issue-bound, ncu 76 % issue-active)
+    __shared__ __align__(16) float2 s12[IMG_IN][IMG_IN + 1];
+    __shared__ __align__(16) float4 hs4[IMG_IN][IMG_T];
+    __shared__ float hs1[IMG_IN][IMG_T];
     __shared__ float red[3][IMG_WARPS];
     const int tid = threadIdx.x, c = blockIdx.z;
     const int x0 = blockIdx.x * IMG_T, y0 = blockIdx.y * IMG_T;
@@ -68,61 +71,64 @@ __global__ void __launch_bounds__(IMG_THREADS) ssim_l1_forward_kernel(
         const int r = i / IMG_IN, q = i - r * IMG_IN;
         const int y = y0 + r - HALO, x = x0 + q - HALO;
         const bool in = (x >= 0) && (x < W) && (y >= 0) && (y < H);   // zero padding (conv2d padding=5)
-        s1[r][q] = in ? p1[(size_t)y * W + x] : 0.f;
-        s2[r][q] = in ? p2[(size_t)y * W + x] : 0.f;
+        s12[r][q] = make_float2(in ? p1[(size_t)y * W + x] : 0.f, in ? p2[(size_t)y * W + x] : 0.f);
     }
     __syncthreads();
     // horizontal pass, register-blocked: one item = IMG_RB consecutive outputs of one row, fed from WIN + IMG_RB - 1
-    // loads per image instead of WIN per output (the pass was shared-memory-bound: ncu LSU pipe 70 %); a warp takes
-    // 8 column groups x 4 rows (row stride 43 words: 32 distinct banks); per output the same operations in the same
-    // order as the one-output-per-thread form
+    // loads instead of WIN per output; a warp takes 8 column groups x 4 rows
     for (int i = tid; i < IMG_IN * (IMG_T / IMG_RB); i += IMG_THREADS) {
         const int r = i / (IMG_T / IMG_RB), q0 = (i - r * (IMG_T / IMG_RB)) * IMG_RB;
-        float xs[WIN + IMG_RB - 1], ys[WIN + IMG_RB - 1];
+        float2 xy[WIN + IMG_RB - 1];
 #pragma unroll
-        for (int t = 0; t < WIN + IMG_RB - 1; ++t) { xs[t] = s1[r][q0 + t]; ys[t] = s2[r][q0 + t]; }
-        float o0[IMG_RB], o1[IMG_RB], o2[IMG_RB], o3[IMG_RB], o4[IMG_RB];
+        for (int t = 0; t < WIN + IMG_RB - 1; ++t) xy[t] = s12[r][q0 + t];
 #pragma unroll
         for (int o = 0; o < IMG_RB; ++o) {
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+            float2 a01 = make_float2(0.f, 0.f), a23 = make_float2(0.f, 0.f);
+            float a4 = 0.f;
 #pragma unroll
             for (int k = 0; k < WIN; ++k) {
-                const float x = xs[o + k], y = ys[o + k];
-                const float wx = win.w[k] * x, wy = win.w[k] * y;
-                a0 += wx;
-                a1 += wy;
-                a2 = fmaf(wx, x, a2);
-                a3 = fmaf(wy, y, a3);
-                a4 = fmaf(wx, y, a4);
+                const float2 v = xy[o + k];
+                const float2 wv = __fmul2_rn(make_float2(win.w[k], win.w[k]), v);      // (w x, w y)
+                a01 = __fadd2_rn(a01, wv);                                            // mu1 += w x; mu2 += w y
+                a23 = __ffma2_rn(wv, v, a23);                                         // E[xx] += (w x) x; E[yy] += (w y) y
+                a4 = fmaf(wv.x, v.y, a4);                                             // E[xy] += (w x) y
             }
-            o0[o] = a0; o1[o] = a1; o2[o] = a2; o3[o] = a3; o4[o] = a4;
+            hs4[r][q0 + o] = make_float4(a01.x, a01.y, a23.x, a23.y);
+            hs1[r][q0 + o] = a4;
         }
-        static_assert(IMG_RB == 4, "the row writes below are one float4 per moment");
-        *reinterpret_cast<float4*>(&hs[0][r][q0]) = make_float4(o0[0], o0[1], o0[2], o0[3]);
-        *reinterpret_cast<float4*>(&hs[1][r][q0]) = make_float4(o1[0], o1[1], o1[2], o1[3]);
-        *reinterpret_cast<float4*>(&hs[2][r][q0]) = make_float4(o2[0], o2[1], o2[2], o2[3]);
-        *reinterpret_cast<float4*>(&hs[3][r][q0]) = make_float4(o3[0], o3[1], o3[2], o3[3]);
-        *reinterpret_cast<float4*>(&hs[4][r][q0]) = make_float4(o4[0], o4[1], o4[2], o4[3]);
     }
     __syncthreads();
-    // vertical pass, register-blocked the same way: a thread owns column tx and the IMG_RB consecutive rows from
-    // IMG_RB * ty (IMG_T / IMG_WARPS == IMG_RB), one moment at a time to keep the live set small
+    // vertical pass: a thread owns column tx and the IMG_RB consecutive rows from IMG_RB * ty; the WIN + IMG_RB - 1 rows
+    // it needs stream through once, each feeding every output whose window covers it (taps in ascending order per
+    // output, as before)
     const int tx = tid & 31, ty = tid >> 5;
     static_assert(IMG_T / IMG_WARPS == IMG_RB, "one thread per column and IMG_RB consecutive rows");
     const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
     float accS = 0.f, accL = 0.f, accN = 0.f;
     float mom[5][IMG_RB];
+    {
+        float2 m01[IMG_RB], m23[IMG_RB];
+        float m4[IMG_RB];
 #pragma unroll
-    for (int m = 0; m < 5; ++m) {
-        float col[WIN + IMG_RB - 1];
+        for (int j = 0; j < IMG_RB; ++j) { m01[j] = make_float2(0.f, 0.f); m23[j] = make_float2(0.f, 0.f); m4[j] = 0.f; }
 #pragma unroll
-        for (int t = 0; t < WIN + IMG_RB - 1; ++t) col[t] = hs[m][IMG_RB * ty + t][tx];
+        for (int t = 0; t < WIN + IMG_RB - 1; ++t) {
+            const float4 h = hs4[IMG_RB * ty + t][tx];
+            const float h4 = hs1[IMG_RB * ty + t][tx];
+#pragma unroll
+            for (int j = 0; j < IMG_RB; ++j) {
+                const int k = t - j;
+                if (k >= 0 && k < WIN) {
+                    const float2 w2 = make_float2(win.w[k], win.w[k]);
+                    m01[j] = __ffma2_rn(w2, make_float2(h.x, h.y), m01[j]);
+                    m23[j] = __ffma2_rn(w2, make_float2(h.z, h.w), m23[j]);
+                    m4[j] = fmaf(win.w[k], h4, m4[j]);
+                }
+            }
+        }
 #pragma unroll
         for (int j = 0; j < IMG_RB; ++j) {
-            float a = 0.f;
-#pragma unroll
-            for (int k = 0; k < WIN; ++k) a = fmaf(win.w[k], col[j + k], a);
-            mom[m][j] = a;
+            mom[0][j] = m01[j].x; mom[1][j] = m01[j].y; mom[2][j] = m23[j].x; mom[3][j] = m23[j].y; mom[4][j] = m4[j];
         }
     }
 #pragma unroll
@@ -140,7 +146,8 @@ __global__ void __launch_bounds__(IMG_THREADS) ssim_l1_forward_kernel(
             const float B1 = mu1_sq + mu2_sq + C1, B2 = sigma1_sq + sigma2_sq + C2;
             const float S = (A1 * A2) / (B1 * B2);
             accS += S * m;
-            const float a = s1[r + HALO][tx + HALO], b = s2[r + HALO][tx + HALO];
+            const float2 ab = s12[r + HALO][tx + HALO];
+            const float a = ab.x, b = ab.y;
             accL += fabsf(a * m - b * m);                      // loss_utils.py:34
             accN += (m == 1.f) ? 1.f : 0.f;                     // torch.sum(mask == 1)
             if (dmap) {
