@@ -7,7 +7,7 @@ from torch.profiler import profile, ProfilerActivity
 import bench
 dev = torch.device("cuda")
 sc, cam, gt = bench.build_workload("B", 0, dev)
-st = bench.Stepper("native", os.environ.get("DIAG_MODE", "dropin"), sc, cam, dev)
+st = bench.make_stepper("native", os.environ.get("DIAG_MODE", "dropin"), sc, cam, dev)
 gt = gt.cuda()
 for _ in range(int(os.environ.get("DIAG_WARM", "15"))):
     st.step(gt)
