@@ -13,14 +13,15 @@
 //                                 per-digit decoupled look-back across tiles (chained scan fused into
 //                                 the scatter pass), smem reorder, coalesced scatter.
 // HBM-bound: algorithmic bytes = n*(sizeof(K)+ (24 per pass for u64/u32 pairs)).
+#include <cstdlib>
+#include <type_traits>
 #include "common.cuh"
 
 namespace r3dgw {
 
 constexpr int OS_THREADS = 256;
 constexpr int OS_WARPS = OS_THREADS / 32;
-constexpr int OS_ITEMS = 16;
-constexpr int OS_TILE = OS_THREADS * OS_ITEMS;   // 4096 pairs per CTA
+constexpr int OS_ITEMS_MIN = 8;                   // smallest tile any instantiation uses (sizes the look-back workspace)
 
 struct SortPasses {
     int n_pass;
@@ -43,10 +44,10 @@ static SortPasses make_passes(int end_bit) {
 }
 
 // workspace layout: hist u32[MAX_PASSES][256] | tile counters u32[MAX_PASSES] (+pad) | status u64[n_pass][tiles][256]
-static inline size_t os_tiles(int n) { return ((size_t)n + OS_TILE - 1) / OS_TILE; }
+static inline size_t os_tiles(int n, int items) { return ((size_t)n + OS_THREADS * items - 1) / (OS_THREADS * items); }
 size_t sort_workspace_bytes(int n) {
     size_t head = SORT_MAX_PASSES * SORT_RADIX * sizeof(uint32_t) + 256;
-    return align_up(head + os_tiles(n) * SORT_RADIX * sizeof(unsigned long long) * SORT_MAX_PASSES, 256);
+    return align_up(head + os_tiles(n, OS_ITEMS_MIN) * SORT_RADIX * sizeof(unsigned long long) * SORT_MAX_PASSES, 256);
 }
 
 template <typename KeyT>
@@ -97,8 +98,9 @@ __device__ __forceinline__ unsigned long long os_status_load(const unsigned long
     return w;
 }
 
-template <typename KeyT>
+template <typename KeyT, int OS_ITEMS>
 struct OsSmem {
+    static constexpr int OS_TILE = OS_THREADS * OS_ITEMS;
     uint32_t warp_hist[OS_WARPS][SORT_RADIX];   // per-warp digit counts, then exclusive-across-warps offsets
     uint32_t digit_start[SORT_RADIX];           // tile-local start of each digit in the reordered tile
     uint32_t bin_offset[SORT_RADIX];            // global position = bin_offset[d] + local position
@@ -108,7 +110,7 @@ struct OsSmem {
     uint32_t vals[OS_TILE];
 };
 
-template <typename KeyT>
+template <typename KeyT, int OS_ITEMS>
 __global__ void __launch_bounds__(OS_THREADS) onesweep_pass_kernel(
     const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, KeyT* __restrict__ keys_out,
     uint32_t* __restrict__ vals_out, int n, int shift, uint32_t mask,
@@ -117,7 +119,8 @@ __global__ void __launch_bounds__(OS_THREADS) onesweep_pass_kernel(
     unsigned long long* __restrict__ status)     // [tiles][256] look-back words
 {
     extern __shared__ __align__(16) unsigned char os_smem_raw[];
-    OsSmem<KeyT>& s = *reinterpret_cast<OsSmem<KeyT>*>(os_smem_raw);
+    constexpr int OS_TILE = OS_THREADS * OS_ITEMS;
+    OsSmem<KeyT, OS_ITEMS>& s = *reinterpret_cast<OsSmem<KeyT, OS_ITEMS>*>(os_smem_raw);
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     if (tid == 0) s.tile_id = atomicAdd(tile_counter, 1u);
@@ -252,7 +255,10 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
     if (n <= 0) return 0;
     SortPasses sp = make_passes(end_bit);
     if (sp.n_pass > SORT_MAX_PASSES) return R3DGW_ERR_UNSUPPORTED;
-    const size_t tiles = os_tiles(n);
+    // pairs per CTA tile = 256 x items: R3DGW_OS_ITEMS = 8 / 12 / 16 (A/B; 16 is the measured default)
+    static const int items = [] { const char* e = getenv("R3DGW_OS_ITEMS"); const int v = e ? atoi(e) : 16;
+                                  return (v == 8 || v == 12) ? v : 16; }();
+    const size_t tiles = os_tiles(n, items);
     uint32_t* hist = reinterpret_cast<uint32_t*>(workspace);
     uint32_t* counters = hist + SORT_MAX_PASSES * SORT_RADIX;
     unsigned long long* status = reinterpret_cast<unsigned long long*>(
@@ -274,19 +280,26 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
     }
     R3DGW_LAUNCH_CHECK();
 
-    static bool attr_set = false;
-    const int smem = (int)sizeof(OsSmem<KeyT>);
-    R3DGW_CUDA_TRY(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    (void)attr_set;
+    auto launch_pass = [&](auto tag, int p, const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout) -> int {
+        constexpr int IT = decltype(tag)::value;
+        const int smem = (int)sizeof(OsSmem<KeyT, IT>);
+        R3DGW_CUDA_TRY(cudaFuncSetAttribute((onesweep_pass_kernel<KeyT, IT>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        onesweep_pass_kernel<KeyT, IT><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
+            kin, vin, kout, vout, n, sp.shift[p], sp.mask[p], hist + p * SORT_RADIX, counters + p,
+            status + (size_t)p * status_per_pass);
+        return 0;
+    };
 
     KeyT* kin = keys_in; KeyT* kout = keys_alt;
     uint32_t* vin = vals_in; uint32_t* vout = vals_alt;
     for (int p = 0; p < sp.n_pass; ++p) {
         {
             ProfScope ps(g_sort_prof_kid >= 0 ? g_sort_prof_kid : KID_SORT_PASS, stream);
-            onesweep_pass_kernel<KeyT><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
-                kin, vin, kout, vout, n, sp.shift[p], sp.mask[p], hist + p * SORT_RADIX, counters + p,
-                status + (size_t)p * status_per_pass);
+            int rc;
+            if (items == 8) rc = launch_pass(std::integral_constant<int, 8>{}, p, kin, vin, kout, vout);
+            else if (items == 12) rc = launch_pass(std::integral_constant<int, 12>{}, p, kin, vin, kout, vout);
+            else rc = launch_pass(std::integral_constant<int, 16>{}, p, kin, vin, kout, vout);
+            if (rc) return rc;
         }
         R3DGW_LAUNCH_CHECK();
         std::swap(kin, kout);
