@@ -110,7 +110,7 @@ struct OsSmem {
     uint32_t vals[OS_TILE];
 };
 
-template <typename KeyT, int OS_ITEMS>
+template <typename KeyT, int OS_ITEMS, bool BALLOT_MATCH = false>
 __global__ void __launch_bounds__(OS_THREADS) onesweep_pass_kernel(
     const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, KeyT* __restrict__ keys_out,
     uint32_t* __restrict__ vals_out, int n, int shift, uint32_t mask,
@@ -152,7 +152,24 @@ __global__ void __launch_bounds__(OS_THREADS) onesweep_pass_kernel(
     for (int i = 0; i < OS_ITEMS; ++i) {
         int g = warp_base + i * 32 + (int)lane;
         uint32_t d = (g < n) ? ((uint32_t)(key[i] >> shift) & mask) : SORT_RADIX;   // sentinel for the tail
-        uint32_t peers = __match_any_sync(0xffffffffu, d);
+        uint32_t peers;
+        if constexpr (BALLOT_MATCH) {
+            // lanes holding the same digit, from 8 + 1 ballots: constant cost, whereas MATCH.ANY iterates over the
+            // distinct values in the warp - and the low tile-id bits of consecutive duplicates are all distinct
+            // (voting only the pass's significant bits, or skipping the validity vote on full tiles, puts uniform branches
+            // into the ranking loop and was measured slower: 0.105 -> 0.114 ms per step)
+            const bool valid = d < SORT_RADIX;
+            const uint32_t bv = __ballot_sync(0xffffffffu, valid);
+            peers = valid ? bv : ~bv;
+#pragma unroll
+            for (int bit = 0; bit < SORT_RADIX_BITS; ++bit) {
+                const bool on = (d >> bit) & 1u;
+                const uint32_t bal = __ballot_sync(0xffffffffu, on);
+                peers &= on ? bal : ~bal;
+            }
+        } else {
+            peers = __match_any_sync(0xffffffffu, d);
+        }
         uint32_t leader = __ffs(peers) - 1;
         uint32_t before = 0;
         if (lane == leader && d < SORT_RADIX) {
@@ -280,11 +297,14 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
     }
     R3DGW_LAUNCH_CHECK();
 
-    auto launch_pass = [&](auto tag, int p, const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout) -> int {
+    // R3DGW_OS_MATCH=any: MATCH.ANY for the in-warp digit match instead of the ballot form (A/B)
+    static const bool ballot_match = [] { const char* e = getenv("R3DGW_OS_MATCH"); return !(e && e[0] == 'a'); }();
+    auto launch_pass = [&](auto tag, auto btag, int p, const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout) -> int {
         constexpr int IT = decltype(tag)::value;
+        constexpr bool BM = decltype(btag)::value;
         const int smem = (int)sizeof(OsSmem<KeyT, IT>);
-        R3DGW_CUDA_TRY(cudaFuncSetAttribute((onesweep_pass_kernel<KeyT, IT>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        onesweep_pass_kernel<KeyT, IT><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
+        R3DGW_CUDA_TRY(cudaFuncSetAttribute((onesweep_pass_kernel<KeyT, IT, BM>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        onesweep_pass_kernel<KeyT, IT, BM><<<(unsigned)tiles, OS_THREADS, smem, stream>>>(
             kin, vin, kout, vout, n, sp.shift[p], sp.mask[p], hist + p * SORT_RADIX, counters + p,
             status + (size_t)p * status_per_pass);
         return 0;
@@ -296,9 +316,10 @@ static int sort_pairs_impl(KeyT* keys_in, KeyT* keys_alt, uint32_t* vals_in, uin
         {
             ProfScope ps(g_sort_prof_kid >= 0 ? g_sort_prof_kid : KID_SORT_PASS, stream);
             int rc;
-            if (items == 8) rc = launch_pass(std::integral_constant<int, 8>{}, p, kin, vin, kout, vout);
-            else if (items == 12) rc = launch_pass(std::integral_constant<int, 12>{}, p, kin, vin, kout, vout);
-            else rc = launch_pass(std::integral_constant<int, 16>{}, p, kin, vin, kout, vout);
+            if (items == 8) rc = launch_pass(std::integral_constant<int, 8>{}, std::true_type{}, p, kin, vin, kout, vout);
+            else if (items == 12) rc = launch_pass(std::integral_constant<int, 12>{}, std::true_type{}, p, kin, vin, kout, vout);
+            else if (ballot_match) rc = launch_pass(std::integral_constant<int, 16>{}, std::true_type{}, p, kin, vin, kout, vout);
+            else rc = launch_pass(std::integral_constant<int, 16>{}, std::false_type{}, p, kin, vin, kout, vout);
             if (rc) return rc;
         }
         R3DGW_LAUNCH_CHECK();
