@@ -9,7 +9,7 @@
 // Structure (one read of the keys for all histograms, then one read + one write per 8-bit pass):
 //   1. radix_histogram_kernel   : per-pass digit histograms (smem atomics, one global flush per block)
 //   2. radix_scan_kernel        : exclusive scan of each pass's 256 bins -> global digit bases
-//   3. onesweep_pass_kernel x n : tile of 4096 pairs per CTA; warp-level match-any ranking (stable),
+//   3. onesweep_pass_kernel x n : tile of 4096 pairs per CTA; warp-level digit match from ballots, ranking (stable),
 //                                 per-digit decoupled look-back across tiles (chained scan fused into
 //                                 the scatter pass), smem reorder, coalesced scatter.
 // HBM-bound: algorithmic bytes = n*(sizeof(K)+ (24 per pass for u64/u32 pairs)).
