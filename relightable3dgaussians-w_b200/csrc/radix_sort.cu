@@ -172,10 +172,8 @@ __global__ void __launch_bounds__(OS_THREADS) onesweep_pass_kernel(
         }
         uint32_t leader = __ffs(peers) - 1;
         uint32_t before = 0;
-        if (lane == leader && d < SORT_RADIX) {
-            before = s.warp_hist[warp][d];
-            s.warp_hist[warp][d] = before + __popc(peers);
-        }
+        if (lane == leader && d < SORT_RADIX)     // one shared-memory atomic instead of a dependent load + store
+            before = atomicAdd(&s.warp_hist[warp][d], (uint32_t)__popc(peers));
         before = __shfl_sync(0xffffffffu, before, leader);
         rank[i] = before + __popc(peers & lt_mask);
         __syncwarp();
