@@ -146,6 +146,22 @@ def test_c_abi_exports_every_declared_symbol(native_lib):
     assert native_lib.r3dgw_get_binning_layout(5, 0, 10, ctypes.byref(BL)) == -1
 
 
+def test_every_environment_switch_is_documented():
+    """Every R3DGW_* variable the package reads (getenv in csrc/, os.environ in the Python side) has a row in
+    INTEGRATION.md's switch table."""
+    pkg = os.path.join(ROOT, "relightable3dgaussians-w_b200")
+    names = set()
+    for pat in ("**/*.cu", "**/*.cuh", "**/*.py"):
+        for path in glob.glob(os.path.join(pkg, pat), recursive=True):
+            src = open(path, errors="ignore").read()
+            names |= set(re.findall(r'getenv\("(R3DGW_[A-Z0-9_]+)"\)', src))
+            names |= set(re.findall(r'environ\.get\("(R3DGW_[A-Z0-9_]+)"', src))
+    assert len(names) >= 10
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    missing = sorted(n for n in names if n not in doc)
+    assert not missing, f"switches without a row in INTEGRATION.md: {missing}"
+
+
 def test_product_path_never_imports_oracle():
     """The product package must not reference oracle/ (a CPU fallback would void parity)."""
     pkg = os.path.join(ROOT, "relightable3dgaussians-w_b200")
